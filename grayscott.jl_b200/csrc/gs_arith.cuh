@@ -1,0 +1,94 @@
+// gs_arith.cuh -- the per-cell Gray-Scott update, in two arithmetics.
+//
+// ARITH_REFERENCE reproduces, rounding for rounding, the expression the reference CPU solver
+// evaluates (src/simulation/Common.jl:13-18 + src/simulation/Simulation_CPU.jl:96-109, with
+// Julia's promotion rules): for Float32 fields the six-neighbour sum,
+// u*v^2 and (F+K)*v are Float32 and everything else Float64; for Float64 fields the same tree
+// in Float64.  Every operation is an explicit round-to-nearest intrinsic, so nvcc can neither
+// contract to FMA nor reassociate: results are bit-identical to the CPU solver.
+//
+// ARITH_NATIVE (Float32 only) evaluates the same formula in Float32 with FMAs; it differs from
+// the reference by ~1 ulp per step and is checked against the north-star tolerance (1e-5).
+//
+// x / 6.0 is computed as q = x*c, r = fma(-6,q,x), q' = fma(r,c,q) with c = RN(1/6): the
+// correctly rounded quotient whenever no intermediate underflows (checked against true
+// division on 3.2e9 random doubles, build/scratch history in DESIGN.md); tiny and zero x take
+// the exact paths below.
+#pragma once
+#include "gs_common.cuh"
+
+namespace gsb {
+
+__device__ __forceinline__ double div6_rn(double x) {
+    const double c = 0x1.5555555555555p-3;  // RN(1/6)
+    const double q = __dmul_rn(x, c);
+    const double r = __fma_rn(-6.0, q, x);
+    double res = __fma_rn(r, c, q);
+    if (fabs(x) < 0x1.0p-800) res = (x == 0.0) ? x : __ddiv_rn(x, 6.0);
+    return res;
+}
+
+// su, sv: the left-folded six-neighbour sums ((((W+E)+S)+N)+D)+U computed in T by the caller.
+// r: noise variate in [-1,1) (ignored unless NOISE).
+
+template <bool NOISE>
+__device__ __forceinline__ void cell_update_ref(float uc, float vc, float su, float sv, double r,
+                                                const Params& p, float& un, float& vn) {
+    const double u64 = (double)uc, v64 = (double)vc;
+    // (Float64(su) - 6.0*Float64(uc)) / 6.0 ; 6.0*uc is exact in Float64, so one FMA == mul, sub
+    const double lap_u = div6_rn(__fma_rn(-6.0, u64, (double)su));
+    const double lap_v = div6_rn(__fma_rn(-6.0, v64, (double)sv));
+    const float uvv = __fmul_rn(uc, __fmul_rn(vc, vc));            // u * v^2       (Float32)
+    const float fkv = __fmul_rn(p.fFK, vc);                        // (F + K) * v   (Float32)
+    double du = __dsub_rn(__dmul_rn(p.Du, lap_u), (double)uvv);
+    du = __dadd_rn(du, __dmul_rn(p.F, __dsub_rn(1.0, u64)));
+    if (NOISE) du = __dadd_rn(du, __dmul_rn(p.noise, r));
+    double dv = __dadd_rn(__dmul_rn(p.Dv, lap_v), (double)uvv);
+    dv = __dsub_rn(dv, (double)fkv);
+    if (!p.dt_is_one) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
+    un = (float)__dadd_rn(u64, du);                                // one rounding on store
+    vn = (float)__dadd_rn(v64, dv);
+}
+
+template <bool NOISE>
+__device__ __forceinline__ void cell_update_ref(double uc, double vc, double su, double sv, double r,
+                                                const Params& p, double& un, double& vn) {
+    const double lap_u = div6_rn(__dsub_rn(su, __dmul_rn(6.0, uc)));
+    const double lap_v = div6_rn(__dsub_rn(sv, __dmul_rn(6.0, vc)));
+    const double uvv = __dmul_rn(uc, __dmul_rn(vc, vc));
+    const double fkv = __dmul_rn(p.FK, vc);
+    double du = __dsub_rn(__dmul_rn(p.Du, lap_u), uvv);
+    du = __dadd_rn(du, __dmul_rn(p.F, __dsub_rn(1.0, uc)));
+    if (NOISE) du = __dadd_rn(du, __dmul_rn(p.noise, r));
+    double dv = __dadd_rn(__dmul_rn(p.Dv, lap_v), uvv);
+    dv = __dsub_rn(dv, fkv);
+    if (!p.dt_is_one) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
+    un = __dadd_rn(uc, du);
+    vn = __dadd_rn(vc, dv);
+}
+
+// Native Float32: same formula, Float32 FMAs.  r32 in [-1,1).
+template <bool NOISE>
+__device__ __forceinline__ void cell_update_native(float uc, float vc, float su, float sv, float r32,
+                                                   const Params& p, float& un, float& vn) {
+    const float sixth = 0x1.555556p-3f;
+    const float lap_u = fmaf(-6.0f, uc, su) * sixth;
+    const float lap_v = fmaf(-6.0f, vc, sv) * sixth;
+    const float uvv = uc * vc * vc;
+    float du = fmaf(p.fDu, lap_u, -uvv);
+    du = fmaf(p.fF, 1.0f - uc, du);
+    if (NOISE) du = fmaf(p.fnoise, r32, du);
+    const float dv = fmaf(p.fDv, lap_v, fmaf(-p.fFK, vc, uvv));
+    un = fmaf(du, p.fdt, uc);
+    vn = fmaf(dv, p.fdt, vc);
+}
+
+// Left-fold neighbour sum in T, the order of Common.jl:14-15: i-1, i+1, j-1, j+1, k-1, k+1.
+__device__ __forceinline__ float sum6(float w, float e, float s, float n, float d, float u) {
+    return __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(w, e), s), n), d), u);
+}
+__device__ __forceinline__ double sum6(double w, double e, double s, double n, double d, double u) {
+    return __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(w, e), s), n), d), u);
+}
+
+}  // namespace gsb

@@ -1,0 +1,81 @@
+// gs_common.cuh -- device-side layout, parameters and small helpers shared by all kernels.
+//
+// Device layout (ours, not the reference's): one subdomain of sx*sy*sz cells with one ghost
+// layer (reference: Array{T,3}(sx+2, sy+2, sz+2), x fastest -- Simulation_CPU.jl:23-28) is
+// stored with a padded row pitch so that interior cell x = 0 sits on a 128-byte boundary:
+//
+//   row:  [ unused ... | W ghost | x=0 ... x=sx-1 | E ghost | pad ... ]
+//           0            xoff-1    xoff                       xoff+sx      < px
+//
+//   xoff = 128 / sizeof(T)            (32 floats / 16 doubles)
+//   px   = round_up(xoff + sx + 1, 128 / sizeof(T))   elements per row
+//   rows = sy + 2, planes = sz + 2    (ghost row/plane first and last, as in the reference)
+//
+// Local coordinates used by the kernels are 0-based interior coordinates: x in [-1, sx],
+// y in [-1, sy], z in [-1, sz]; -1 and s are the ghost layers (reference indices 1 and s+2).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace gsb {
+
+struct Layout {
+    int sx, sy, sz;      // interior sizes (mcd.proc_sizes, communication.jl:73)
+    int xoff;            // element index of interior x = 0 within a row
+    long long px;        // row pitch in elements
+    long long pxy;       // plane pitch in elements = px * (sy + 2)
+
+    __host__ __device__ long long idx(int x, int y, int z) const {
+        return (long long)(xoff + x) + px * (long long)(y + 1) + pxy * (long long)(z + 1);
+    }
+    __host__ __device__ long long elems() const { return pxy * (long long)(sz + 2); }
+};
+
+inline Layout make_layout(int sx, int sy, int sz, size_t elem_size) {
+    Layout l;
+    l.sx = sx; l.sy = sy; l.sz = sz;
+    const int line = (int)(128 / elem_size);
+    l.xoff = line;
+    l.px = ((long long)(l.xoff + sx + 1) + line - 1) / line * line;
+    l.pxy = l.px * (long long)(sy + 2);
+    return l;
+}
+
+// Physics + noise parameters, prepared on the host exactly as calculate! does
+// (Simulation_CPU.jl:82-87: every Settings value is first rounded to T).
+struct Params {
+    // reference arithmetic: T-rounded values widened to double
+    double Du, Dv, F, dt, noise;
+    double FK;           // (F + K) added in T, then widened   (Simulation_CPU.jl:105)
+    // native Float32 arithmetic
+    float fDu, fDv, fF, fFK, fdt, fnoise;
+    int dt_is_one;       // dt == 1 exactly: x * dt == x, multiply skipped (bit-identical)
+    // noise: Philox4x32-10 keyed on (seed, step, global cell)
+    unsigned seed_lo, seed_hi, step;
+    int gx0, gy0, gz0;   // global 0-based coordinate of local interior cell (0,0,0) = proc_offsets
+};
+
+// A box of interior cells [x0,x1) x [y0,y1) x [z0,z1) to update (interior / shell split).
+struct Box {
+    int x0, x1, y0, y1, z0, z1;
+};
+
+enum : int { ARITH_REFERENCE = 0, ARITH_NATIVE = 1 };
+
+// 16-byte vector of T: float x4 or double x2.
+template <typename T>
+struct alignas(16) Vec {
+    static constexpr int N = 16 / sizeof(T);
+    T a[N];
+};
+
+template <typename T>
+__device__ __forceinline__ Vec<T> ld_vec(const T* p) {
+    return *reinterpret_cast<const Vec<T>*>(p);
+}
+template <typename T>
+__device__ __forceinline__ void st_vec(T* p, const Vec<T>& v) {
+    *reinterpret_cast<Vec<T>*>(p) = v;
+}
+
+}  // namespace gsb

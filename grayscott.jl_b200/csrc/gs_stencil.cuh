@@ -1,0 +1,309 @@
+// gs_stencil.cuh -- fused 7-point-Laplacian + Gray-Scott reaction kernels for sm_100a.
+//
+// Replaces calculate! (src/simulation/Simulation_CPU.jl:77-113; superseded GPU versions:
+// ext/CUDAExt.jl:135-186, src/simulation/Simulation_KA.jl:177-235 -- thread <-> z mapping,
+// uncoalesced, 256x over-launched).  Here x (the contiguous dimension) maps to lanes, every
+// thread owns one 16-byte vector of x-consecutive cells (4 floats / 2 doubles), marches along z
+// and keeps the z-1 / z / z+1 vectors of u and v in registers, so each field is read once and
+// written once per step.
+//
+// Three kernels:
+//   stencil_tma_kernel   xy tiles of each z plane staged in shared memory by TMA
+//                        (cp.async.bulk.tensor.3d + mbarrier ring, producer warp), the headline
+//   stencil_l1_kernel    same marching, y neighbours fetched through L1; no shared memory
+//   naive_reflayout_kernel   one thread per cell on arrays in the REFERENCE layout
+//                        (unpadded (s+2)^3), for callers that own such device arrays
+#pragma once
+#include <cuda.h>
+
+#include "gs_arith.cuh"
+#include "gs_common.cuh"
+#include "gs_philox.cuh"
+
+namespace gsb {
+
+// Update the N cells of one vector.  *m/*0/*p: centre vectors at z-1/z/z+1; *s/*n: rows y-1/y+1
+// at z; *w/*e: the scalars left of a[0] and right of a[N-1] at z.
+template <typename T, int ARITH, bool NOISE>
+__device__ __forceinline__ void update_vec(const Vec<T>& um, const Vec<T>& u0, const Vec<T>& up,
+                                           const Vec<T>& us, const Vec<T>& un, T uw, T ue,
+                                           const Vec<T>& vm, const Vec<T>& v0, const Vec<T>& vp,
+                                           const Vec<T>& vs, const Vec<T>& vn, T vw, T ve,
+                                           const Params& p, int x, int y, int z, Vec<T>& uo, Vec<T>& vo) {
+    constexpr int N = Vec<T>::N;
+    unsigned words[N];
+    if (NOISE) noise_words<N>(p, (unsigned)(p.gx0 + x), (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), words);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const T uW = i == 0 ? uw : u0.a[i == 0 ? 0 : i - 1];
+        const T uE = i == N - 1 ? ue : u0.a[i == N - 1 ? i : i + 1];
+        const T vW = i == 0 ? vw : v0.a[i == 0 ? 0 : i - 1];
+        const T vE = i == N - 1 ? ve : v0.a[i == N - 1 ? i : i + 1];
+        const T su = sum6(uW, uE, us.a[i], un.a[i], um.a[i], up.a[i]);
+        const T sv = sum6(vW, vE, vs.a[i], vn.a[i], vm.a[i], vp.a[i]);
+        if constexpr (ARITH == ARITH_NATIVE) {
+            float r32 = 0.f;
+            if (NOISE) r32 = noise_r32(words[i]);
+            cell_update_native<NOISE>(u0.a[i], v0.a[i], su, sv, r32, p, uo.a[i], vo.a[i]);
+        } else {
+            double r = 0.0;
+            if (NOISE) r = noise_r64(words[i]);
+            cell_update_ref<NOISE>(u0.a[i], v0.a[i], su, sv, r, p, uo.a[i], vo.a[i]);
+        }
+    }
+}
+
+// Store the cells of a vector that fall inside [bx0, bx1).
+template <typename T>
+__device__ __forceinline__ void store_masked(T* pu, T* pv, const Vec<T>& uo, const Vec<T>& vo, int x, int bx0,
+                                             int bx1) {
+    constexpr int N = Vec<T>::N;
+    if (x >= bx0 && x + N <= bx1) {
+        st_vec(pu, uo);
+        st_vec(pv, vo);
+    } else {
+#pragma unroll
+        for (int i = 0; i < N; ++i)
+            if (x + i >= bx0 && x + i < bx1) { pu[i] = uo.a[i]; pv[i] = vo.a[i]; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// L1 variant.  block = (32, TY); warp <-> one row; grid = (x tiles, y tiles, z chunks).
+// ------------------------------------------------------------------------------------------
+template <typename T, int ARITH, bool NOISE, int TY>
+__global__ void __launch_bounds__(32 * TY)
+stencil_l1_kernel(const T* __restrict__ u, const T* __restrict__ v, T* __restrict__ uo, T* __restrict__ vo,
+                  const Layout L, const Params p, const Box box, const int zchunk) {
+    constexpr int N = Vec<T>::N;
+    const int lane = threadIdx.x;
+    const int xt0 = (box.x0 / N) * N;  // vectors are aligned to the absolute grid
+    const int x = xt0 + (blockIdx.x * 32 + lane) * N;
+    const int y = box.y0 + blockIdx.y * TY + threadIdx.y;
+    const int zs = box.z0 + blockIdx.z * zchunk;
+    const int ze = min(zs + zchunk, box.z1);
+    if (y >= box.y1 || zs >= ze) return;                 // whole warp leaves together
+    const bool loadable = (long long)(L.xoff + x + N) <= L.px;
+    const bool lane_w = lane == 0, lane_e = lane == 31;
+    const long long pxy = L.pxy, px = L.px;
+
+    Vec<T> zero;
+#pragma unroll
+    for (int i = 0; i < N; ++i) zero.a[i] = T(0);
+
+    const long long base = loadable ? L.idx(x, y, zs) : L.idx(0, y, zs);
+    const T* pu = u + base;
+    const T* pv = v + base;
+    Vec<T> um = loadable ? ld_vec(pu - pxy) : zero, vm = loadable ? ld_vec(pv - pxy) : zero;
+    Vec<T> u0 = loadable ? ld_vec(pu) : zero, v0 = loadable ? ld_vec(pv) : zero;
+    Vec<T> up = loadable ? ld_vec(pu + pxy) : zero, vp = loadable ? ld_vec(pv + pxy) : zero;
+
+    for (int z = zs; z < ze; ++z) {
+        // prefetch the centre of plane z+2 (needed next iteration); plane index <= sz exists
+        Vec<T> upp = zero, vpp = zero;
+        if (loadable && z + 1 < ze) { upp = ld_vec(pu + 2 * pxy); vpp = ld_vec(pv + 2 * pxy); }
+        Vec<T> us = zero, un = zero, vs = zero, vn = zero;
+        if (loadable) {
+            us = ld_vec(pu - px); un = ld_vec(pu + px);
+            vs = ld_vec(pv - px); vn = ld_vec(pv + px);
+        }
+        T uw = __shfl_up_sync(0xffffffffu, u0.a[N - 1], 1);
+        T ue = __shfl_down_sync(0xffffffffu, u0.a[0], 1);
+        T vw = __shfl_up_sync(0xffffffffu, v0.a[N - 1], 1);
+        T ve = __shfl_down_sync(0xffffffffu, v0.a[0], 1);
+        if (lane_w && loadable) { uw = pu[-1]; vw = pv[-1]; }
+        if (lane_e && loadable) { ue = pu[N]; ve = pv[N]; }   // row padding guarantees this address
+        if (loadable && x < box.x1 && x + N > box.x0) {
+            Vec<T> ou, ov;
+            update_vec<T, ARITH, NOISE>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, x, y, z, ou, ov);
+            store_masked(uo + (pu - u), vo + (pv - v), ou, ov, x, box.x0, box.x1);
+        }
+        um = u0; u0 = up; up = upp;
+        vm = v0; v0 = vp; vp = vpp;
+        pu += pxy; pv += pxy;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// TMA variant.
+//
+// CTA = TY consumer warps (one tile row each) + 1 producer warp.  For every plane of its z chunk
+// (plus the two halo planes) the producer issues two cp.async.bulk.tensor.3d loads -- the
+// (32N + 2N) x (TY + 2) x 1 box of u and of v, x halo = one whole 16-byte vector each side so the
+// centre stays 16-byte aligned in shared memory -- into a ring of STAGES slots, completion on a
+// per-slot "full" mbarrier.  Consumers keep centre z-1/z/z+1 in registers, read the y+-1 rows and
+// the two x edge scalars from the slot of plane z, compute, store with 16-byte coalesced st.global
+// and release the slot on its "empty" mbarrier (one arrive per consumer warp).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, int c0, int c1, int c2,
+                                            unsigned bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+
+template <typename T, int TY>
+struct TmaTile {
+    static constexpr int N = Vec<T>::N;
+    static constexpr int BW = 32 * N + 2 * N;                       // box width in elements (544 B)
+    static constexpr int ROWS = TY + 2;
+    static constexpr int BOX_BYTES = BW * ROWS * (int)sizeof(T);
+    static constexpr int FIELD_BYTES = (BOX_BYTES + 127) / 128 * 128;  // TMA dst alignment
+    static constexpr int STAGE_BYTES = 2 * FIELD_BYTES;
+    static constexpr size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 128 + 16 * stages; }
+};
+
+template <typename T, int ARITH, bool NOISE, int TY, int STAGES>
+__global__ void __launch_bounds__(32 * (TY + 1))
+stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_v,
+                   T* __restrict__ uo, T* __restrict__ vo, const Layout L, const Params p, const Box box,
+                   const int zchunk) {
+    using Tile = TmaTile<T, TY>;
+    constexpr int N = Tile::N;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    // carve: [stages][2 fields][FIELD_BYTES] | full[STAGES] | empty[STAGES]
+    unsigned char* tiles = (unsigned char*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
+    unsigned long long* bars = (unsigned long long*)(tiles + (size_t)STAGES * Tile::STAGE_BYTES);
+    const unsigned bar0 = smem_u32(bars);
+    auto full_bar = [&](int s) { return bar0 + 8u * (unsigned)s; };
+    auto empty_bar = [&](int s) { return bar0 + 8u * (unsigned)(STAGES + s); };
+
+    const int lane = threadIdx.x, w = threadIdx.y;
+    const int xt0 = (box.x0 / N) * N;
+    const int xtile = xt0 + blockIdx.x * 32 * N;         // first interior x of this tile
+    const int ytile = box.y0 + blockIdx.y * TY;          // first interior y of this tile
+    const int zs = box.z0 + blockIdx.z * zchunk;
+    const int ze = min(zs + zchunk, box.z1);
+    const int nplanes = ze - zs + 2;                     // zs-1 .. ze
+
+    if (w == 0 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), TY); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (w == TY) {
+        // ------------------------------ producer warp ------------------------------
+        if (lane == 0) {
+            const int c0 = L.xoff + xtile - N;           // element index in row
+            const int c1 = ytile;                        // row index of y = ytile-1
+            for (int i = 0; i < nplanes; ++i) {
+                const int s = i % STAGES;
+                mbar_wait(empty_bar(s), ((i / STAGES) & 1) ^ 1);
+                mbar_expect_tx(full_bar(s), 2u * (unsigned)Tile::BOX_BYTES);
+                const unsigned dst = smem_u32(tiles + (size_t)s * Tile::STAGE_BYTES);
+                const int c2 = zs + i;                   // plane index of z = zs-1+i
+                tma_load_3d(dst, &map_u, c0, c1, c2, full_bar(s));
+                tma_load_3d(dst + Tile::FIELD_BYTES, &map_v, c0, c1, c2, full_bar(s));
+            }
+        }
+        return;
+    }
+
+    // ------------------------------ consumer warps ------------------------------
+    const int x = xtile + lane * N;
+    const int y = ytile + w;
+    const bool row_active = y < box.y1;
+    const bool vec_active = row_active && x < box.x1 && x + N > box.x0;
+    const long long out0 = vec_active ? L.idx(x, y, zs) : 0;
+    T* pou = uo + out0;
+    T* pov = vo + out0;
+
+    Vec<T> um, u0, up, vm, v0, vp;
+#pragma unroll
+    for (int i = 0; i < N; ++i) { um.a[i] = u0.a[i] = up.a[i] = vm.a[i] = v0.a[i] = vp.a[i] = T(0); }
+
+    for (int i = 0; i < nplanes; ++i) {
+        const int s = i % STAGES;
+        mbar_wait(full_bar(s), (i / STAGES) & 1);
+        const T* su_ = (const T*)(tiles + (size_t)s * Tile::STAGE_BYTES);
+        const T* sv_ = (const T*)(tiles + (size_t)s * Tile::STAGE_BYTES + Tile::FIELD_BYTES);
+        const int roff = (w + 1) * Tile::BW + N + lane * N;     // my centre vector in the box
+        up = ld_vec(su_ + roff);
+        vp = ld_vec(sv_ + roff);
+        if (i >= 2) {
+            const int sp = (i - 1) % STAGES;                      // slot holding plane z
+            const T* pu_ = (const T*)(tiles + (size_t)sp * Tile::STAGE_BYTES);
+            const T* pv_ = (const T*)(tiles + (size_t)sp * Tile::STAGE_BYTES + Tile::FIELD_BYTES);
+            const Vec<T> us = ld_vec(pu_ + roff - Tile::BW), un = ld_vec(pu_ + roff + Tile::BW);
+            const Vec<T> vs = ld_vec(pv_ + roff - Tile::BW), vn = ld_vec(pv_ + roff + Tile::BW);
+            T uw = __shfl_up_sync(0xffffffffu, u0.a[N - 1], 1);
+            T ue = __shfl_down_sync(0xffffffffu, u0.a[0], 1);
+            T vw = __shfl_up_sync(0xffffffffu, v0.a[N - 1], 1);
+            T ve = __shfl_down_sync(0xffffffffu, v0.a[0], 1);
+            if (lane == 0) { uw = pu_[roff - 1]; vw = pv_[roff - 1]; }
+            if (lane == 31) { ue = pu_[roff + N]; ve = pv_[roff + N]; }
+            if (vec_active) {
+                const int z = zs + i - 2;
+                Vec<T> ou, ov;
+                update_vec<T, ARITH, NOISE>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, x, y, z, ou, ov);
+                store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
+                pou += L.pxy; pov += L.pxy;
+            }
+        }
+        if (i >= 1) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty_bar((i - 1) % STAGES));
+        }
+        um = u0; u0 = up;
+        vm = v0; v0 = vp;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Naive kernel on the reference layout: arrays are (sx+2)(sy+2)(sz+2), x fastest, no padding
+// (what a CuArray-owning caller has).  One thread per cell, x <-> threadIdx.x (coalesced).
+// ------------------------------------------------------------------------------------------
+template <typename T, int ARITH, bool NOISE>
+__global__ void __launch_bounds__(256)
+naive_reflayout_kernel(const T* __restrict__ u, const T* __restrict__ v, T* __restrict__ uo, T* __restrict__ vo,
+                       const int sx, const int sy, const int sz, const Params p) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    const int z = blockIdx.z;
+    if (x >= sx || y >= sy || z >= sz) return;
+    const long long nx = sx + 2, nxy = nx * (long long)(sy + 2);
+    const long long c = (x + 1) + nx * (long long)(y + 1) + nxy * (long long)(z + 1);
+    const T uc = u[c], vc = v[c];
+    const T su = sum6(u[c - 1], u[c + 1], u[c - nx], u[c + nx], u[c - nxy], u[c + nxy]);
+    const T sv = sum6(v[c - 1], v[c + 1], v[c - nx], v[c + nx], v[c - nxy], v[c + nxy]);
+    unsigned word = 0;
+    if (NOISE) {
+        const unsigned gx = (unsigned)(p.gx0 + x);
+        Philox4 ph = philox4x32_10(gx >> 2, (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), p.step, p.seed_lo, p.seed_hi);
+        const unsigned sel = gx & 3u;
+        word = sel == 0 ? ph.w[0] : sel == 1 ? ph.w[1] : sel == 2 ? ph.w[2] : ph.w[3];
+    }
+    T un, vn;
+    if constexpr (ARITH == ARITH_NATIVE) {
+        cell_update_native<NOISE>(uc, vc, su, sv, NOISE ? noise_r32(word) : 0.f, p, un, vn);
+    } else {
+        cell_update_ref<NOISE>(uc, vc, su, sv, NOISE ? noise_r64(word) : 0.0, p, un, vn);
+    }
+    uo[c] = un;
+    vo[c] = vn;
+}
+
+}  // namespace gsb

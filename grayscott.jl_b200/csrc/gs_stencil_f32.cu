@@ -1,0 +1,9 @@
+// Float32 instantiations of the stencil kernels (see gs_stencil.cuh).
+#include "gs_stencil_launch.inc"
+namespace gsb {
+template cudaError_t launch_stencil_T<float>(const StencilCfg&, const void*, const void*, void*, void*,
+                                             const CUtensorMap*, const CUtensorMap*, const Layout&, const Params&,
+                                             const Box&, cudaStream_t);
+template cudaError_t launch_naive_T<float>(int, int, const void*, const void*, void*, void*, int, int, int,
+                                           const Params&, cudaStream_t);
+}  // namespace gsb

@@ -1,0 +1,734 @@
+// gsb200_api.cu -- the C ABI of include/gsb200.h: handle, streams, ping-pong buffers, step
+// orchestration (interior / shell overlap with the halo exchange), NCCL and in-process
+// transports.  Kernels live in gs_stencil.cuh / gs_kernels.cu.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "../../include/gsb200.h"
+#include "gs_kernels.h"
+
+using namespace gsb;
+
+// ------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+
+static int fail(const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CK(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess)                                                                        \
+            return fail("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));        \
+    } while (0)
+
+// ------------------------------------------------------------------ NCCL, loaded lazily
+// dlopen instead of a link-time dependency: a process that already holds an NCCL (PyTorch's
+// bundled one) must keep exactly that copy.
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+
+static int nccl_load() {
+    if (g_nccl.lib) return 0;
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return fail("cannot load libnccl.so.2: %s", dlerror());
+#define SYM(field, name)                                                       \
+    *(void**)(&g_nccl.field) = dlsym(lib, name);                               \
+    if (!g_nccl.field) return fail("libnccl: missing symbol %s", name);
+    SYM(GetUniqueId, "ncclGetUniqueId")
+    SYM(CommInitRank, "ncclCommInitRank")
+    SYM(CommDestroy, "ncclCommDestroy")
+    SYM(Send, "ncclSend")
+    SYM(Recv, "ncclRecv")
+    SYM(GroupStart, "ncclGroupStart")
+    SYM(GroupEnd, "ncclGroupEnd")
+    SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+    g_nccl.lib = lib;
+    return 0;
+}
+
+#define NK(call)                                                                                      \
+    do {                                                                                              \
+        ncclResult_t r_ = (call);                                                                     \
+        if (r_ != ncclSuccess)                                                                        \
+            return fail("%s:%d: %s -> %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r_));     \
+    } while (0)
+
+// ------------------------------------------------------------------ handle
+enum : int { TR_NONE = 0, TR_LOCAL = 1, TR_NCCL = 2 };
+
+struct gsb_handle {
+    gsb_config cfg;
+    Layout L;
+    size_t es;
+    int device;
+    long long global[3];
+    void* f[4];             // bound as u, v, u_temp, v_temp (swap exchanges 0<->2, 1<->3)
+    CUtensorMap map[4];     // tensor map of f[i] for the current TMA tile height
+    int map_ty;             // tile height the maps were encoded for (0 = none)
+    cudaStream_t s_compute, s_comm;
+    cudaEvent_t ev_compute, ev_halo, ev_packed;
+    long long step;
+    StencilCfg kcfg;
+    // halo
+    bool active[6];
+    int n_active;
+    void* send[6];
+    void* recv[2][6];       // double-buffered by step parity
+    int transport;
+    gsb_handle* peer[6];
+    ncclComm_t comm;
+    // scratch for gsb_field_stats
+    double* stats_partials;
+    double* stats_out;
+    // timers
+    int timers_on;
+    cudaEvent_t tev[6];     // comm begin/end, compute begin, interior end, compute end, (spare)
+    bool timers_valid;
+    long long launches;     // kernels launched by this handle (bench.py's gpu_launches)
+};
+
+static inline int opp(int d) { return d ^ 1; }
+
+static Params make_params(const gsb_handle* h) {
+    const gsb_config& c = h->cfg;
+    Params p;
+    memset(&p, 0, sizeof p);
+    if (c.dtype == GSB_F32) {
+        const float Du = (float)c.Du, Dv = (float)c.Dv, F = (float)c.F, K = (float)c.k, dt = (float)c.dt,
+                    nz = (float)c.noise;                     // convert(T, settings.x)  Simulation_CPU.jl:82-87
+        const float FK = F + K;                              // Float32 add, :105
+        p.Du = Du; p.Dv = Dv; p.F = F; p.dt = dt; p.noise = nz; p.FK = FK;
+        p.fDu = Du; p.fDv = Dv; p.fF = F; p.fFK = FK; p.fdt = dt; p.fnoise = nz;
+        p.dt_is_one = dt == 1.0f;
+    } else {
+        p.Du = c.Du; p.Dv = c.Dv; p.F = c.F; p.dt = c.dt; p.noise = c.noise; p.FK = c.F + c.k;
+        p.fDu = (float)c.Du; p.fDv = (float)c.Dv; p.fF = (float)c.F; p.fFK = (float)(c.F + c.k);
+        p.fdt = (float)c.dt; p.fnoise = (float)c.noise;
+        p.dt_is_one = c.dt == 1.0;
+    }
+    p.seed_lo = (unsigned)(c.seed & 0xffffffffu);
+    p.seed_hi = (unsigned)(c.seed >> 32);
+    p.step = (unsigned)h->step;
+    p.gx0 = (int)c.offsets[0]; p.gy0 = (int)c.offsets[1]; p.gz0 = (int)c.offsets[2];
+    return p;
+}
+
+static int ensure_maps(gsb_handle* h) {
+    if (h->kcfg.kind != KERNEL_TMA) return 0;
+    if (h->map_ty == h->kcfg.ty) return 0;
+    for (int i = 0; i < 4; ++i) {
+        const char* err = nullptr;
+        if (make_field_tensor_map(&h->map[i], h->cfg.dtype, h->f[i], h->L, h->kcfg.ty, &err))
+            return fail("tensor map: %s", err ? err : "?");
+    }
+    h->map_ty = h->kcfg.ty;
+    return 0;
+}
+
+static void swap_bindings(gsb_handle* h) {
+    std::swap(h->f[0], h->f[2]);
+    std::swap(h->f[1], h->f[3]);
+    std::swap(h->map[0], h->map[2]);
+    std::swap(h->map[1], h->map[3]);
+    h->step += 1;
+}
+
+static bool kernel_shape_ok(const StencilCfg& k) {
+    return k.kind == KERNEL_TMA
+               ? ((k.ty == 8 && (k.stages == 4 || k.stages == 6)) || (k.ty == 16 && (k.stages == 3 || k.stages == 4)))
+               : (k.ty == 4 || k.ty == 8);
+}
+
+static int parse_kernel_env(StencilCfg* k) {
+    const char* e = getenv("GSB_KERNEL");
+    if (!e || !*e) return 0;
+    char kind[16] = {0};
+    int ty = 0, st = 0, zc = 0;
+    const int n = sscanf(e, "%15[^:]:%d:%d:%d", kind, &ty, &st, &zc);
+    if (n < 1) return fail("GSB_KERNEL: expected kind:ty:stages:zchunk, got '%s'", e);
+    if (!strcmp(kind, "tma")) k->kind = KERNEL_TMA;
+    else if (!strcmp(kind, "l1")) k->kind = KERNEL_L1;
+    else return fail("GSB_KERNEL: unknown kind '%s' (tma|l1)", kind);
+    if (n >= 2 && ty > 0) k->ty = ty;
+    if (n >= 3 && st > 0) k->stages = st;
+    if (n >= 4 && zc > 0) k->zchunk = zc;
+    if (!kernel_shape_ok(*k)) return fail("GSB_KERNEL='%s': shape is not instantiated", e);
+    return 0;
+}
+
+// ------------------------------------------------------------------ lifetime
+extern "C" int gsb_version(void) { return GSB_VERSION; }
+extern "C" const char* gsb_last_error(void) { return g_err.c_str(); }
+
+extern "C" int gsb_dims_create(int n, int32_t dims[3]) {
+    if (n < 1) return fail("gsb_dims_create: nranks must be >= 1");
+    dims[0] = dims[1] = dims[2] = 1;
+    int f[64], nf = 0, m = n;
+    for (int p = 2; p * p <= m; ++p) while (m % p == 0) { f[nf++] = p; m /= p; }
+    if (m > 1) f[nf++] = m;
+    for (int i = nf - 1; i >= 0; --i) {
+        int s = 0;
+        for (int d = 1; d < 3; ++d) if (dims[d] < dims[s]) s = d;
+        dims[s] *= f[i];
+    }
+    for (int a = 0; a < 3; ++a) for (int b = a + 1; b < 3; ++b) if (dims[b] > dims[a]) std::swap(dims[a], dims[b]);
+    return 0;
+}
+
+extern "C" int gsb_fill_domain(gsb_config* c, int64_t L, int nranks, int rank) {
+    if (!c) return fail("gsb_fill_domain: null config");
+    if (rank < 0 || rank >= nranks) return fail("gsb_fill_domain: rank %d outside [0,%d)", rank, nranks);
+    if (gsb_dims_create(nranks, c->dims)) return 1;
+    c->L = L; c->rank = rank; c->nranks = nranks;
+    const int dy = c->dims[1], dz = c->dims[2];
+    c->coords[0] = rank / (dy * dz); c->coords[1] = (rank / dz) % dy; c->coords[2] = rank % dz;  // row-major
+    for (int d = 0; d < 3; ++d) {
+        if (L % c->dims[d] != 0)
+            return fail("L = %lld does not divide by dims[%d] = %d (reference: InexactError, communication.jl:73)",
+                        (long long)L, d, c->dims[d]);
+        c->global[d] = L;
+        c->sizes[d] = L / c->dims[d];
+        c->offsets[d] = c->sizes[d] * c->coords[d];
+    }
+    auto rk = [&](int cx, int cy, int cz) -> int {
+        if (cx < 0 || cy < 0 || cz < 0 || cx >= c->dims[0] || cy >= c->dims[1] || cz >= c->dims[2]) return -1;
+        return (cx * dy + cy) * dz + cz;
+    };
+    const int cx = c->coords[0], cy = c->coords[1], cz = c->coords[2];
+    c->neighbors[GSB_WEST] = rk(cx - 1, cy, cz); c->neighbors[GSB_EAST] = rk(cx + 1, cy, cz);
+    c->neighbors[GSB_DOWN] = rk(cx, cy - 1, cz); c->neighbors[GSB_UP] = rk(cx, cy + 1, cz);
+    c->neighbors[GSB_SOUTH] = rk(cx, cy, cz - 1); c->neighbors[GSB_NORTH] = rk(cx, cy, cz + 1);
+    return 0;
+}
+
+extern "C" int gsb_destroy(gsb_t* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    if (h->comm && g_nccl.lib) g_nccl.CommDestroy(h->comm);
+    for (int i = 0; i < 4; ++i) if (h->f[i]) cudaFree(h->f[i]);
+    for (int d = 0; d < 6; ++d) {
+        if (h->send[d]) cudaFree(h->send[d]);
+        for (int q = 0; q < 2; ++q) if (h->recv[q][d]) cudaFree(h->recv[q][d]);
+    }
+    if (h->stats_partials) cudaFree(h->stats_partials);
+    if (h->stats_out) cudaFree(h->stats_out);
+    if (h->s_compute) cudaStreamDestroy(h->s_compute);
+    if (h->s_comm) cudaStreamDestroy(h->s_comm);
+    if (h->ev_compute) cudaEventDestroy(h->ev_compute);
+    if (h->ev_halo) cudaEventDestroy(h->ev_halo);
+    if (h->ev_packed) cudaEventDestroy(h->ev_packed);
+    for (int i = 0; i < 6; ++i) if (h->tev[i]) cudaEventDestroy(h->tev[i]);
+    delete h;
+    return 0;
+}
+
+static int create_impl(gsb_handle* h, const gsb_config* cfg) {
+    h->cfg = *cfg;
+    const gsb_config& c = h->cfg;
+    if (c.dtype != GSB_F32 && c.dtype != GSB_F64) return fail("dtype must be GSB_F32 or GSB_F64");
+    if (c.arith != GSB_ARITH_REFERENCE && c.arith != GSB_ARITH_NATIVE) return fail("unknown arith %d", c.arith);
+    if (c.arith == GSB_ARITH_NATIVE && c.dtype != GSB_F32) return fail("GSB_ARITH_NATIVE exists for Float32 only");
+    for (int d = 0; d < 3; ++d) {
+        if (c.sizes[d] < 1 || c.sizes[d] > (1 << 30)) return fail("sizes[%d] = %lld out of range", d, (long long)c.sizes[d]);
+        h->global[d] = c.global[d] > 0 ? c.global[d] : c.L;
+        if (h->global[d] < 1) return fail("L / global extent must be >= 1");
+        if (h->global[d] % 2 != 0)
+            return fail("global extent %lld is odd (reference: Int64(L/2 - 6) raises InexactError, Simulation_CPU.jl:34)",
+                        (long long)h->global[d]);
+        if (c.offsets[d] < 0 || c.offsets[d] + c.sizes[d] > h->global[d])
+            return fail("offsets[%d] + sizes[%d] exceeds the global extent", d, d);
+        if (h->global[d] >= (1ll << 32)) return fail("global extent too large for the 32-bit noise counter");
+    }
+    h->es = c.dtype == GSB_F32 ? 4 : 8;
+    h->device = c.device;
+    CK(cudaSetDevice(h->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, h->device));
+    if (prop.major < 10) return fail("device %d is sm_%d%d; this library holds sm_100a code only", h->device, prop.major, prop.minor);
+    h->L = make_layout((int)c.sizes[0], (int)c.sizes[1], (int)c.sizes[2], h->es);
+    const size_t bytes = (size_t)h->L.elems() * h->es;
+    for (int i = 0; i < 4; ++i) CK(cudaMalloc(&h->f[i], bytes));
+    CK(cudaStreamCreateWithFlags(&h->s_compute, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->s_comm, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_compute, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_halo, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_packed, cudaEventDisableTiming));
+    for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&h->tev[i]));
+    h->n_active = 0;
+    for (int d = 0; d < 6; ++d) {
+        h->active[d] = c.neighbors[d] >= 0;
+        if (h->active[d]) {
+            h->n_active++;
+            const size_t fb = 2 * (size_t)face_elems(h->L, d) * h->es;
+            CK(cudaMalloc(&h->send[d], fb));
+            CK(cudaMalloc(&h->recv[0][d], fb));
+            CK(cudaMalloc(&h->recv[1][d], fb));
+        }
+    }
+    CK(cudaMalloc(&h->stats_partials, sizeof(double) * (size_t)stats_scratch_doubles()));
+    CK(cudaMalloc(&h->stats_out, sizeof(double) * 5));
+    h->kcfg.dtype = c.dtype; h->kcfg.arith = c.arith; h->kcfg.noise = c.noise != 0.0;
+    h->kcfg.kind = KERNEL_TMA; h->kcfg.ty = 8; h->kcfg.stages = 4; h->kcfg.zchunk = 64;
+    if (parse_kernel_env(&h->kcfg)) return 1;
+    return ensure_maps(h);
+}
+
+extern "C" int gsb_create(gsb_t** out, const gsb_config* cfg) {
+    if (!out || !cfg) return fail("gsb_create: null argument");
+    *out = nullptr;
+    gsb_handle* h = new gsb_handle();
+    memset((void*)h, 0, sizeof *h);
+    if (create_impl(h, cfg)) {
+        std::string keep = g_err;
+        gsb_destroy(h);
+        g_err = keep;
+        return 1;
+    }
+    *out = h;
+    return 0;
+}
+
+// ------------------------------------------------------------------ init / access
+extern "C" int gsb_init_fields(gsb_t* h) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    const long long off[3] = {h->cfg.offsets[0], h->cfg.offsets[1], h->cfg.offsets[2]};
+    CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+    CK(launch_init_fields(h->cfg.dtype, h->f[0], h->f[1], h->f[2], h->f[3], h->L, h->global, off, h->s_compute));
+    CK(cudaEventRecord(h->ev_compute, h->s_compute));
+    h->step = 0;
+    return 0;
+}
+
+extern "C" int gsb_sync(gsb_t* h) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->s_comm));
+    CK(cudaStreamSynchronize(h->s_compute));
+    return 0;
+}
+
+// strided copy between the padded device array and a dense host array (g = 1: with ghosts)
+static int copy_field(gsb_handle* h, void* dev, void* host, int g, bool to_host) {
+    const Layout& L = h->L;
+    cudaMemcpy3DParms p;
+    memset(&p, 0, sizeof p);
+    const size_t nx = (size_t)(L.sx + 2 * g), ny = (size_t)(L.sy + 2 * g), nz = (size_t)(L.sz + 2 * g);
+    // no CUDA array takes part: every x quantity is in bytes
+    cudaPitchedPtr dptr = make_cudaPitchedPtr(dev, (size_t)L.px * h->es, (size_t)L.px * h->es, (size_t)(L.sy + 2));
+    cudaPitchedPtr hptr = make_cudaPitchedPtr(host, nx * h->es, nx * h->es, ny);
+    cudaPos dpos = make_cudaPos((size_t)(L.xoff - g) * h->es, (size_t)(1 - g), (size_t)(1 - g));
+    cudaPos hpos = make_cudaPos(0, 0, 0);
+    p.extent = make_cudaExtent(nx * h->es, ny, nz);
+    if (to_host) { p.srcPtr = dptr; p.srcPos = dpos; p.dstPtr = hptr; p.dstPos = hpos; p.kind = cudaMemcpyDeviceToHost; }
+    else { p.srcPtr = hptr; p.srcPos = hpos; p.dstPtr = dptr; p.dstPos = dpos; p.kind = cudaMemcpyHostToDevice; }
+    CK(cudaMemcpy3DAsync(&p, h->s_compute));
+    return 0;
+}
+
+extern "C" int gsb_get_fields(gsb_t* h, void* u_host, void* v_host) {
+    if (!h || !u_host || !v_host) return fail("gsb_get_fields: null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->s_comm));
+    if (copy_field(h, h->f[0], u_host, 0, true)) return 1;
+    if (copy_field(h, h->f[1], v_host, 0, true)) return 1;
+    CK(cudaStreamSynchronize(h->s_compute));
+    return 0;
+}
+
+extern "C" int gsb_get_ghosted(gsb_t* h, int which, void* host) {
+    if (!h || !host) return fail("gsb_get_ghosted: null argument");
+    if (which < 0 || which > 3) return fail("gsb_get_ghosted: which = %d", which);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->s_comm));
+    if (copy_field(h, h->f[which], host, 1, true)) return 1;
+    CK(cudaStreamSynchronize(h->s_compute));
+    return 0;
+}
+
+extern "C" int gsb_set_ghosted(gsb_t* h, int which, const void* host) {
+    if (!h || !host) return fail("gsb_set_ghosted: null argument");
+    if (which < 0 || which > 3) return fail("gsb_set_ghosted: which = %d", which);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->s_comm));
+    if (copy_field(h, h->f[which], const_cast<void*>(host), 1, false)) return 1;
+    CK(cudaEventRecord(h->ev_compute, h->s_compute));
+    CK(cudaStreamSynchronize(h->s_compute));
+    return 0;
+}
+
+extern "C" int gsb_alloc_host(void** out, size_t bytes) {
+    if (!out) return fail("gsb_alloc_host: null argument");
+    CK(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    return 0;
+}
+extern "C" int gsb_free_host(void* p) {
+    if (p) CK(cudaFreeHost(p));
+    return 0;
+}
+
+extern "C" int gsb_get_step(gsb_t* h, int64_t* step) {
+    if (!h || !step) return fail("null argument");
+    *step = h->step;
+    return 0;
+}
+extern "C" int gsb_set_step(gsb_t* h, int64_t step) {
+    if (!h) return fail("null handle");
+    h->step = step;
+    return 0;
+}
+
+extern "C" int gsb_field_stats(gsb_t* h, int which, double thresh, double out[5]) {
+    if (!h || !out) return fail("null argument");
+    if (which < 0 || which > 3) return fail("gsb_field_stats: which = %d", which);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->s_comm));
+    CK(launch_field_stats(h->cfg.dtype, h->f[which], h->L, thresh, h->stats_partials, h->stats_out, h->s_compute));
+    CK(cudaMemcpyAsync(out, h->stats_out, sizeof(double) * 5, cudaMemcpyDeviceToHost, h->s_compute));
+    CK(cudaStreamSynchronize(h->s_compute));
+    return 0;
+}
+
+// ------------------------------------------------------------------ kernel selection, timers
+extern "C" int gsb_set_kernel(gsb_t* h, int kind, int ty, int stages, int zchunk) {
+    if (!h) return fail("null handle");
+    StencilCfg k = h->kcfg;
+    if (kind == GSB_KERNEL_TMA || kind == GSB_KERNEL_L1) k.kind = kind;
+    else if (kind >= 0) return fail("unknown kernel kind %d", kind);
+    if (ty > 0) k.ty = ty;
+    if (stages > 0) k.stages = stages;
+    if (zchunk > 0) k.zchunk = zchunk;
+    if (!kernel_shape_ok(k)) return fail("kernel shape kind=%d ty=%d stages=%d is not instantiated", k.kind, k.ty, k.stages);
+    CK(cudaSetDevice(h->device));
+    h->kcfg = k;
+    return ensure_maps(h);
+}
+extern "C" int gsb_get_kernel(gsb_t* h, int* kind, int* ty, int* stages, int* zchunk) {
+    if (!h) return fail("null handle");
+    if (kind) *kind = h->kcfg.kind;
+    if (ty) *ty = h->kcfg.ty;
+    if (stages) *stages = h->kcfg.stages;
+    if (zchunk) *zchunk = h->kcfg.zchunk;
+    return 0;
+}
+extern "C" int gsb_timers_enable(gsb_t* h, int on) {
+    if (!h) return fail("null handle");
+    h->timers_on = on;
+    h->timers_valid = false;
+    return 0;
+}
+extern "C" int gsb_timers(gsb_t* h, double out_ms[4]) {
+    if (!h || !out_ms) return fail("null argument");
+    if (!h->timers_on || !h->timers_valid) return fail("gsb_timers: enable timers and run gsb_step first");
+    if (gsb_sync(h)) return 1;
+    float a = 0, b = 0, c = 0, d = 0;
+    if (h->n_active) CK(cudaEventElapsedTime(&a, h->tev[0], h->tev[1]));
+    CK(cudaEventElapsedTime(&b, h->tev[2], h->tev[3]));
+    CK(cudaEventElapsedTime(&c, h->tev[3], h->tev[4]));
+    CK(cudaEventElapsedTime(&d, h->tev[2], h->tev[4]));
+    out_ms[0] = a; out_ms[1] = b; out_ms[2] = c; out_ms[3] = d;
+    return 0;
+}
+extern "C" int gsb_halo_bytes(gsb_t* h, int64_t* bytes) {
+    if (!h || !bytes) return fail("null argument");
+    long long b = 0;
+    for (int d = 0; d < 6; ++d) if (h->active[d]) b += 2 * face_elems(h->L, d) * (long long)h->es;
+    *bytes = b;
+    return 0;
+}
+extern "C" int gsb_launch_count(gsb_t* h, int64_t* count) {
+    if (!h || !count) return fail("null argument");
+    *count = h->launches;
+    return 0;
+}
+extern "C" int gsb_compute_stream(gsb_t* h, void** stream) {
+    if (!h || !stream) return fail("null argument");
+    *stream = (void*)h->s_compute;
+    return 0;
+}
+
+// ------------------------------------------------------------------ communication set-up
+extern "C" int gsb_get_unique_id(void* id128) {
+    if (!id128) return fail("null argument");
+    if (nccl_load()) return 1;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    NK(g_nccl.GetUniqueId(&id));
+    memcpy(id128, &id, sizeof id);
+    return 0;
+}
+
+extern "C" int gsb_comm_init(gsb_t* h, const void* id128) {
+    if (!h || !id128) return fail("null argument");
+    if (h->transport != TR_NONE) return fail("communication already initialised");
+    if (nccl_load()) return 1;
+    CK(cudaSetDevice(h->device));
+    ncclUniqueId id;
+    memcpy(&id, id128, sizeof id);
+    NK(g_nccl.CommInitRank(&h->comm, h->cfg.nranks, id, h->cfg.rank));
+    h->transport = TR_NCCL;
+    return 0;
+}
+
+extern "C" int gsb_comm_init_local(gsb_t** hs, int n) {
+    if (!hs || n < 1) return fail("gsb_comm_init_local: bad arguments");
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r]) return fail("gsb_comm_init_local: null handle %d", r);
+        if (hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r)
+            return fail("gsb_comm_init_local: hs[%d] has rank %d of %d", r, hs[r]->cfg.rank, hs[r]->cfg.nranks);
+        if (hs[r]->transport != TR_NONE) return fail("communication already initialised");
+    }
+    for (int r = 0; r < n; ++r) {
+        gsb_handle* h = hs[r];
+        for (int d = 0; d < 6; ++d) {
+            h->peer[d] = nullptr;
+            if (!h->active[d]) continue;
+            const int q = h->cfg.neighbors[d];
+            if (q < 0 || q >= n) return fail("rank %d: neighbour %d out of range", r, q);
+            gsb_handle* p = hs[q];
+            if (p->cfg.neighbors[opp(d)] != r) return fail("rank %d and %d disagree about being neighbours", r, q);
+            if (face_elems(p->L, opp(d)) != face_elems(h->L, d)) return fail("rank %d and %d: face sizes differ", r, q);
+            h->peer[d] = p;
+            if (p->device != h->device) {
+                int can = 0;
+                CK(cudaDeviceCanAccessPeer(&can, h->device, p->device));
+                if (!can) return fail("device %d cannot access device %d", h->device, p->device);
+                CK(cudaSetDevice(h->device));
+                cudaError_t e = cudaDeviceEnablePeerAccess(p->device, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                else CK(e);
+            }
+        }
+    }
+    for (int r = 0; r < n; ++r) hs[r]->transport = TR_LOCAL;
+    return 0;
+}
+
+// ------------------------------------------------------------------ step orchestration
+static Box full_box(const gsb_handle* h) { return Box{0, h->L.sx, 0, h->L.sy, 0, h->L.sz}; }
+
+static int launch_box(gsb_handle* h, const Box& b, const Params& p) {
+    CK(launch_stencil(h->kcfg, h->f[0], h->f[1], h->f[2], h->f[3], &h->map[0], &h->map[1], h->L, p, b, h->s_compute));
+    h->launches += 1;
+    return 0;
+}
+
+// thickness of the shell (cells next to an exchanged face) per axis: one tile
+static void shell_thickness(const gsb_handle* h, int t[3]) {
+    t[0] = 32 * (int)(16 / h->es);
+    t[1] = h->kcfg.ty;
+    t[2] = 1;
+}
+
+// the part of the update that reads no exchanged ghost cell
+static bool interior_box(const gsb_handle* h, Box* b) {
+    int t[3];
+    shell_thickness(h, t);
+    const int s[3] = {h->L.sx, h->L.sy, h->L.sz};
+    int lo[3], hi[3];
+    for (int d = 0; d < 3; ++d) {
+        lo[d] = h->active[2 * d] ? t[d] : 0;
+        hi[d] = h->active[2 * d + 1] ? s[d] - t[d] : s[d];
+        if (hi[d] <= lo[d]) return false;
+    }
+    *b = Box{lo[0], hi[0], lo[1], hi[1], lo[2], hi[2]};
+    return true;
+}
+
+// pack -> (transport) : first half of exchange!, on the comm stream
+static int enqueue_pack_send(gsb_handle* h) {
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamWaitEvent(h->s_comm, h->ev_compute, 0));       // current fields are final
+    if (h->timers_on) CK(cudaEventRecord(h->tev[0], h->s_comm));
+    const int par = (int)(h->step & 1);
+    FaceSet fs;
+    fs.n = 0;
+    for (int d = 0; d < 6; ++d) {
+        if (!h->active[d]) continue;
+        fs.dir[fs.n] = d;
+        fs.buf[fs.n] = h->transport == TR_LOCAL ? h->peer[d]->recv[par][opp(d)] : h->send[d];
+        fs.n++;
+    }
+    CK(launch_pack_faces(h->cfg.dtype, h->f[0], h->f[1], h->L, fs, h->s_comm));
+    h->launches += 1;
+    if (h->transport == TR_NCCL) {
+        const ncclDataType_t ty = h->cfg.dtype == GSB_F32 ? ncclFloat : ncclDouble;
+        NK(g_nccl.GroupStart());
+        for (int d = 0; d < 6; ++d) {
+            if (!h->active[d]) continue;
+            const size_t cnt = 2 * (size_t)face_elems(h->L, d);
+            NK(g_nccl.Send(h->send[d], cnt, ty, h->cfg.neighbors[d], h->comm, h->s_comm));
+            NK(g_nccl.Recv(h->recv[par][d], cnt, ty, h->cfg.neighbors[d], h->comm, h->s_comm));
+        }
+        NK(g_nccl.GroupEnd());
+    }
+    CK(cudaEventRecord(h->ev_packed, h->s_comm));
+    return 0;
+}
+
+// (wait for the neighbours) -> unpack : second half of exchange!
+static int enqueue_unpack(gsb_handle* h) {
+    CK(cudaSetDevice(h->device));
+    const int par = (int)(h->step & 1);
+    if (h->transport == TR_LOCAL)
+        for (int d = 0; d < 6; ++d)
+            if (h->active[d]) CK(cudaStreamWaitEvent(h->s_comm, h->peer[d]->ev_packed, 0));
+    FaceSet fs;
+    fs.n = 0;
+    for (int d = 0; d < 6; ++d) {
+        if (!h->active[d]) continue;
+        fs.dir[fs.n] = d;
+        fs.buf[fs.n] = h->recv[par][d];
+        fs.n++;
+    }
+    CK(launch_unpack_faces(h->cfg.dtype, h->f[0], h->f[1], h->L, fs, h->s_comm));
+    h->launches += 1;
+    if (h->timers_on) CK(cudaEventRecord(h->tev[1], h->s_comm));
+    CK(cudaEventRecord(h->ev_halo, h->s_comm));
+    return 0;
+}
+
+static int check_transport(gsb_handle* h) {
+    if (h->n_active && h->transport == TR_NONE)
+        return fail("rank %d has neighbours but no transport: call gsb_comm_init or gsb_comm_init_local", h->cfg.rank);
+    return 0;
+}
+
+// interior now, shell after the halo arrived
+static int enqueue_compute_overlapped(gsb_handle* h) {
+    CK(cudaSetDevice(h->device));
+    if (ensure_maps(h)) return 1;
+    const Params p = make_params(h);
+    if (h->timers_on) CK(cudaEventRecord(h->tev[2], h->s_compute));
+    Box in;
+    const bool split = h->n_active > 0 && interior_box(h, &in);
+    if (!split) {
+        if (h->n_active) CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+        if (h->timers_on) CK(cudaEventRecord(h->tev[3], h->s_compute));
+        if (launch_box(h, full_box(h), p)) return 1;
+    } else {
+        if (launch_box(h, in, p)) return 1;
+        if (h->timers_on) CK(cudaEventRecord(h->tev[3], h->s_compute));
+        CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+        const int sx = h->L.sx, sy = h->L.sy, sz = h->L.sz;
+        // disjoint slabs: z slabs span everything, y slabs the interior z range, x slabs the interior y,z range
+        if (in.z0 > 0) if (launch_box(h, Box{0, sx, 0, sy, 0, in.z0}, p)) return 1;
+        if (in.z1 < sz) if (launch_box(h, Box{0, sx, 0, sy, in.z1, sz}, p)) return 1;
+        if (in.y0 > 0) if (launch_box(h, Box{0, sx, 0, in.y0, in.z0, in.z1}, p)) return 1;
+        if (in.y1 < sy) if (launch_box(h, Box{0, sx, in.y1, sy, in.z0, in.z1}, p)) return 1;
+        if (in.x0 > 0) if (launch_box(h, Box{0, in.x0, in.y0, in.y1, in.z0, in.z1}, p)) return 1;
+        if (in.x1 < sx) if (launch_box(h, Box{in.x1, sx, in.y0, in.y1, in.z0, in.z1}, p)) return 1;
+    }
+    if (h->timers_on) { CK(cudaEventRecord(h->tev[4], h->s_compute)); h->timers_valid = true; }
+    CK(cudaEventRecord(h->ev_compute, h->s_compute));
+    return 0;
+}
+
+extern "C" int gsb_exchange(gsb_t* h) {
+    if (!h) return fail("null handle");
+    if (!h->n_active) return 0;
+    if (check_transport(h)) return 1;
+    if (h->transport == TR_LOCAL) return fail("gsb_exchange: in-process handles advance together, use gsb_step_group");
+    if (enqueue_pack_send(h)) return 1;
+    return enqueue_unpack(h);
+}
+
+extern "C" int gsb_calculate(gsb_t* h) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    if (ensure_maps(h)) return 1;
+    const Params p = make_params(h);
+    if (h->n_active) CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+    if (launch_box(h, full_box(h), p)) return 1;
+    CK(cudaEventRecord(h->ev_compute, h->s_compute));
+    return 0;
+}
+
+extern "C" int gsb_swap(gsb_t* h) {
+    if (!h) return fail("null handle");
+    swap_bindings(h);
+    return 0;
+}
+
+extern "C" int gsb_step(gsb_t* h, int nsteps) {
+    if (!h) return fail("null handle");
+    if (nsteps < 0) return fail("nsteps < 0");
+    if (check_transport(h)) return 1;
+    if (h->transport == TR_LOCAL) return fail("gsb_step: in-process handles advance together, use gsb_step_group");
+    for (int s = 0; s < nsteps; ++s) {
+        if (h->n_active) {
+            if (enqueue_pack_send(h)) return 1;
+            if (enqueue_unpack(h)) return 1;
+        }
+        if (enqueue_compute_overlapped(h)) return 1;
+        swap_bindings(h);
+    }
+    return 0;
+}
+
+extern "C" int gsb_step_group(gsb_t** hs, int n, int nsteps) {
+    if (!hs || n < 1) return fail("gsb_step_group: bad arguments");
+    if (nsteps < 0) return fail("nsteps < 0");
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r]) return fail("null handle %d", r);
+        if (check_transport(hs[r])) return 1;
+        if (hs[r]->n_active && hs[r]->transport != TR_LOCAL) return fail("gsb_step_group needs gsb_comm_init_local");
+        if (hs[r]->step != hs[0]->step) return fail("handles are at different steps");
+    }
+    for (int s = 0; s < nsteps; ++s) {
+        for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_pack_send(hs[r])) return 1;
+        for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_unpack(hs[r])) return 1;
+        for (int r = 0; r < n; ++r) if (enqueue_compute_overlapped(hs[r])) return 1;
+        for (int r = 0; r < n; ++r) swap_bindings(hs[r]);
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ stateless kernel entry
+extern "C" int gsb_calculate_arrays(int dtype, int arith, const int64_t sizes[3], const int64_t offsets[3],
+                                    const void* u_dev, const void* v_dev, void* u_out_dev, void* v_out_dev,
+                                    double Du, double Dv, double F, double k, double dt, double noise,
+                                    uint64_t seed, uint32_t step, void* stream) {
+    if (!sizes || !offsets || !u_dev || !v_dev || !u_out_dev || !v_out_dev) return fail("gsb_calculate_arrays: null argument");
+    if (dtype != GSB_F32 && dtype != GSB_F64) return fail("dtype must be GSB_F32 or GSB_F64");
+    if (arith == GSB_ARITH_NATIVE && dtype != GSB_F32) return fail("GSB_ARITH_NATIVE exists for Float32 only");
+    for (int d = 0; d < 3; ++d)
+        if (sizes[d] < 1 || sizes[d] > (1 << 30)) return fail("sizes[%d] out of range", d);
+    if (sizes[2] > 65535) return fail("sizes[2] > 65535 is not supported by this entry point");
+    gsb_handle tmp;
+    memset((void*)&tmp, 0, sizeof tmp);
+    tmp.cfg.dtype = dtype; tmp.cfg.Du = Du; tmp.cfg.Dv = Dv; tmp.cfg.F = F; tmp.cfg.k = k; tmp.cfg.dt = dt;
+    tmp.cfg.noise = noise; tmp.cfg.seed = seed; tmp.step = step;
+    for (int d = 0; d < 3; ++d) tmp.cfg.offsets[d] = offsets[d];
+    const Params p = make_params(&tmp);
+    CK(launch_naive_reflayout(dtype, arith, noise != 0.0, u_dev, v_dev, u_out_dev, v_out_dev, (int)sizes[0],
+                              (int)sizes[1], (int)sizes[2], p, (cudaStream_t)stream));
+    return 0;
+}

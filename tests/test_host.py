@@ -1,0 +1,149 @@
+"""CPU tests of the boundary and the host-side mirror: the C-ABI library loads and exports every
+symbol include/gsb200.h declares, Settings/TOML/domain logic follow the reference, and the
+multi-process plumbing works over gloo with world_size 2.  No compute call needs a GPU here."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+import pytest
+
+from conftest import PHYS, ROOT
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    header = open(os.path.join(ROOT, "include", "gsb200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(gsb_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 30
+    lib = C.CDLL(pkg.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in gsb200.h but not exported"
+    assert declared == set(pkg.SYMBOLS), declared ^ set(pkg.SYMBOLS)
+    assert pkg._lib.lib().gsb_version() == 100
+
+
+def test_product_never_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under grayscott.jl_b200/ may name it."""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "grayscott.jl_b200")):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".inc")):
+                text = open(os.path.join(dirpath, fn)).read()
+                assert "gs_oracle" not in text.replace("oracle/gs_oracle.c holds the same definition", "")
+                assert "import oracle" not in text and "from oracle" not in text
+
+
+def test_settings_defaults_and_toml(sim, tmp_path):
+    s = sim.Settings()
+    # Structs.jl:5-27
+    assert (s.L, s.steps, s.plotgap, s.F, s.k, s.dt, s.Du, s.Dv, s.noise) == (128, 20000, 200, 0.04, 0, 0.2, 0.05, 0.1, 0.0)
+    assert (s.precision, s.backend, s.kernel_language) == ("Float64", "CPU", "Plain")
+    toml = textwrap.dedent("""
+        L = 64
+        Du = 0.2
+        Dv = 0.1
+        F = 0.02
+        k = 0.048
+        dt = 1.0
+        plotgap = 10
+        steps = 1000
+        noise = 0.1
+        output = "gs-1MPI-1GPU-64L-F32.bp"
+        adios_config = "adios2.yaml"
+        precision = "Float32"
+        backend = "B200"
+    """)
+    s = sim.parse_settings_toml(toml)                 # unknown key adios_config ignored (Inputs.jl:88-94)
+    assert (s.L, s.steps, s.noise, s.precision, s.backend) == (64, 1000, 0.1, "Float32", "B200")
+    assert not hasattr(s, "adios_config")
+    assert sim.load_backend_and_lang(s) == ("b200", "plain")
+    p = tmp_path / "cfg.toml"
+    p.write_text(toml)
+    assert sim.get_settings([str(p)]).L == 64
+    with pytest.raises(ValueError, match="TOML"):     # unit-Inputs.jl:11: non-.toml -> ArgumentError
+        sim.get_settings(["cfg.json"])
+
+
+def test_unsupported_backend_message(sim):
+    s = sim.Settings(backend="CUDA", kernel_language="KernelAbstractions")
+    mcd = sim.init_domain(s, 0, 1)
+    with pytest.raises(sim.GsbError, match="Backend :cuda and kernel language :kernelabstractions not supported."):
+        sim.init_fields(s, mcd, "Float32")
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 4, 8, 6])
+def test_init_domain_matches_oracle(sim, orc, nranks):
+    L = 24
+    s = sim.Settings(L=L)
+    o = orc.Oracle(L, "Float32", dims=orc.dims_create(nranks), **PHYS)
+    for r in range(nranks):
+        mcd = sim.init_domain(s, r, nranks)
+        info = o.rank_info(r)
+        assert mcd.dims == o.dims and mcd.coords == info["coords"]
+        assert mcd.proc_sizes == info["sizes"] and mcd.proc_offsets == info["offsets"]
+        assert tuple(mcd.proc_neighbors[n] for n in ("west", "east", "down", "up", "south", "north")) == info["neighbors"]
+
+
+def test_uneven_L_is_an_error(sim):
+    with pytest.raises(sim.GsbError, match="does not divide"):
+        sim.init_domain(sim.Settings(L=10), 0, 3)          # dims (3,1,1)
+
+
+def test_no_gpu_fails_loudly(sim):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    s = sim.Settings(L=8, backend="B200", precision="Float32")
+    with pytest.raises(sim.GsbError):
+        sim.init_fields(s, sim.init_domain(s, 0, 1), "Float32")
+
+
+_WORKER = r"""
+import os, sys
+sys.path.insert(0, {root!r})
+import torch, torch.distributed as dist
+import __graft_entry__ as entry
+sim = entry.load_package().simulation
+rank, ws = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:{port}", rank=rank, world_size=ws)
+s = sim.Settings(L=16, backend="B200", precision="Float64")
+mcd = sim.init_domain(s, rank, ws)
+# every rank learns every rank's view; neighbour relations must be mutual and faces must match
+views = [None] * ws
+dist.all_gather_object(views, dict(rank=rank, sizes=mcd.proc_sizes, offsets=mcd.proc_offsets, nbr=mcd.proc_neighbors))
+opp = dict(west="east", east="west", down="up", up="down", south="north", north="south")
+for v in views:
+    for name, q in v["nbr"].items():
+        if q >= 0:
+            assert views[q]["nbr"][opp[name]] == v["rank"]
+assert mcd.dims == (2, 1, 1) and mcd.proc_sizes == (8, 16, 16)
+# the 128-byte id travels like broadcast_unique_id's payload
+t = torch.arange(128, dtype=torch.uint8) if rank == 0 else torch.zeros(128, dtype=torch.uint8)
+dist.broadcast(t, src=0)
+assert bytes(t.tolist()) == bytes(range(128))
+# weak-sharded throughput bookkeeping of bench.py: max over ranks
+ms = torch.tensor([1.0 + rank], dtype=torch.float64)
+dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+assert ms.item() == float(ws)
+dist.barrier()
+dist.destroy_process_group()
+print("worker", rank, "ok")
+"""
+
+
+def test_gloo_world_size_2(tmp_path):
+    port = 29500 + os.getpid() % 2000
+    script = tmp_path / "worker.py"
+    script.write_text(_WORKER.format(root=ROOT, port=port))
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    for p in procs:
+        out, _ = p.communicate(timeout=240)
+        assert p.returncode == 0, out
+        assert "ok" in out
