@@ -28,8 +28,16 @@ __device__ __forceinline__ double div6_rn(double x) {
     return res;
 }
 
+// noise * r with r = ri * 2^-31, ri the integer-valued variate of gs_philox.cuh.  Scaling by a
+// power of two is exact, so RN(noise * r) == RN((noise * 2^-31) * ri) unless noise * 2^-31 leaves
+// the normal range; the host decides (Params::noise_fast) and both paths give the same bits.
+__device__ __forceinline__ double noise_term(const Params& p, double ri) {
+    return p.noise_fast ? __dmul_rn(p.noise_s, ri) : __dmul_rn(p.noise, __dmul_rn(ri, 0x1.0p-31));
+}
+
 // su, sv: the left-folded six-neighbour sums ((((W+E)+S)+N)+D)+U computed in T by the caller.
-// r: noise variate in [-1,1) (ignored unless NOISE).
+// r: integer-valued noise variate ri in [-2^31, 2^31) (reference) / r32 in [-1,1) (native); ignored
+// unless NOISE.
 
 template <bool NOISE>
 __device__ __forceinline__ void cell_update_ref(float uc, float vc, float su, float sv, double r,
@@ -42,7 +50,7 @@ __device__ __forceinline__ void cell_update_ref(float uc, float vc, float su, fl
     const float fkv = __fmul_rn(p.fFK, vc);                        // (F + K) * v   (Float32)
     double du = __dsub_rn(__dmul_rn(p.Du, lap_u), (double)uvv);
     du = __dadd_rn(du, __dmul_rn(p.F, __dsub_rn(1.0, u64)));
-    if (NOISE) du = __dadd_rn(du, __dmul_rn(p.noise, r));
+    if (NOISE) du = __dadd_rn(du, noise_term(p, r));
     double dv = __dadd_rn(__dmul_rn(p.Dv, lap_v), (double)uvv);
     dv = __dsub_rn(dv, (double)fkv);
     if (!p.dt_is_one) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
@@ -59,7 +67,7 @@ __device__ __forceinline__ void cell_update_ref(double uc, double vc, double su,
     const double fkv = __dmul_rn(p.FK, vc);
     double du = __dsub_rn(__dmul_rn(p.Du, lap_u), uvv);
     du = __dadd_rn(du, __dmul_rn(p.F, __dsub_rn(1.0, uc)));
-    if (NOISE) du = __dadd_rn(du, __dmul_rn(p.noise, r));
+    if (NOISE) du = __dadd_rn(du, noise_term(p, r));
     double dv = __dadd_rn(__dmul_rn(p.Dv, lap_v), uvv);
     dv = __dsub_rn(dv, fkv);
     if (!p.dt_is_one) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
@@ -71,14 +79,14 @@ __device__ __forceinline__ void cell_update_ref(double uc, double vc, double su,
 template <bool NOISE>
 __device__ __forceinline__ void cell_update_native(float uc, float vc, float su, float sv, float r32,
                                                    const Params& p, float& un, float& vn) {
-    const float sixth = 0x1.555556p-3f;
-    const float lap_u = fmaf(-6.0f, uc, su) * sixth;
-    const float lap_v = fmaf(-6.0f, vc, sv) * sixth;
+    // 1/6 of the Laplacian is folded into the diffusion coefficients (fDu6 = Du/6, fDv6 = Dv/6)
+    const float lap6_u = fmaf(-6.0f, uc, su);
+    const float lap6_v = fmaf(-6.0f, vc, sv);
     const float uvv = uc * vc * vc;
-    float du = fmaf(p.fDu, lap_u, -uvv);
+    float du = fmaf(p.fDu6, lap6_u, -uvv);
     du = fmaf(p.fF, 1.0f - uc, du);
     if (NOISE) du = fmaf(p.fnoise, r32, du);
-    const float dv = fmaf(p.fDv, lap_v, fmaf(-p.fFK, vc, uvv));
+    const float dv = fmaf(p.fDv6, lap6_v, fmaf(-p.fFK, vc, uvv));
     un = fmaf(du, p.fdt, uc);
     vn = fmaf(dv, p.fdt, vc);
 }

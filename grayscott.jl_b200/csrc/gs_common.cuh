@@ -47,8 +47,11 @@ struct Params {
     // reference arithmetic: T-rounded values widened to double
     double Du, Dv, F, dt, noise;
     double FK;           // (F + K) added in T, then widened   (Simulation_CPU.jl:105)
+    double noise_s;      // noise * 2^-31 (exactly), valid when noise_fast
+    int noise_fast;
     // native Float32 arithmetic
     float fDu, fDv, fF, fFK, fdt, fnoise;
+    float fDu6, fDv6;    // Du/6, Dv/6
     int dt_is_one;       // dt == 1 exactly: x * dt == x, multiply skipped (bit-identical)
     // noise: Philox4x32-10 keyed on (seed, step, global cell)
     unsigned seed_lo, seed_hi, step;

@@ -9,7 +9,7 @@
 namespace gsb {
 
 enum : int { DT_F32 = 0, DT_F64 = 1 };
-enum : int { KERNEL_TMA = 0, KERNEL_L1 = 1 };
+enum : int { KERNEL_TMA = 0, KERNEL_L1 = 1, KERNEL_TMA_LO = 2, KERNEL_TMA_HI = 3 };
 
 struct StencilCfg {
     int dtype;     // DT_F32 / DT_F64

@@ -35,8 +35,9 @@ __device__ __forceinline__ Philox4 philox4x32_10(unsigned c0, unsigned c1, unsig
 }
 
 __device__ __forceinline__ double noise_r64(unsigned word) {
-    // -1 + 2*(word * 2^-32): every step exact in Float64
-    return __dadd_rn(-1.0, __dmul_rn(2.0, __dmul_rn((double)word, 0x1.0p-32)));
+    // r = -1 + 2*(word * 2^-32) = ri * 2^-31 with ri = word - 2^31; returns ri (exact), the caller
+    // applies the 2^-31 (gs_arith.cuh noise_term)
+    return (double)(int)(word ^ 0x80000000u);
 }
 __device__ __forceinline__ float noise_r32(unsigned word) {
     return (float)((int)(word ^ 0x80000000u) >> 8) * 0x1.0p-23f;

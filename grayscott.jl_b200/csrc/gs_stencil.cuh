@@ -174,18 +174,58 @@ struct TmaTile {
     static constexpr size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 128 + 16 * stages; }
 };
 
-template <typename T, int ARITH, bool NOISE, int TY, int STAGES>
-__global__ void __launch_bounds__(32 * (TY + 1))
+// One consumer iteration: plane index i of the chunk has landed in slot `cur`; am/a0 (bm/b0) hold
+// the centre vectors of planes i-2 / i-1, ap (bp) receives plane i; plane i-1 sits in slot `prev`.
+// The caller rotates the register names (three-way unrolled loop), so no register moves.
+template <typename T, int ARITH, bool NOISE, int TY>
+__device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsigned char* prev, int i,
+                                            const Vec<T>& am, const Vec<T>& a0, Vec<T>& ap, const Vec<T>& bm,
+                                            const Vec<T>& b0, Vec<T>& bp, const int roff, const int eoff,
+                                            const bool lane_w, const bool lane_e, const bool vec_active,
+                                            const Params& p, const Box& box, const int x, const int y, const int z,
+                                            T*& pou, T*& pov, const long long pxy) {
+    using Tile = TmaTile<T, TY>;
+    constexpr int N = Tile::N;
+    const T* su_ = reinterpret_cast<const T*>(cur);
+    const T* sv_ = reinterpret_cast<const T*>(cur + Tile::FIELD_BYTES);
+    ap = ld_vec(su_ + roff);
+    bp = ld_vec(sv_ + roff);
+    if (i >= 2) {
+        const T* pu_ = reinterpret_cast<const T*>(prev);
+        const T* pv_ = reinterpret_cast<const T*>(prev + Tile::FIELD_BYTES);
+        const Vec<T> us = ld_vec(pu_ + roff - Tile::BW), un = ld_vec(pu_ + roff + Tile::BW);
+        const Vec<T> vs = ld_vec(pv_ + roff - Tile::BW), vn = ld_vec(pv_ + roff + Tile::BW);
+        // x neighbours across vectors: shuffles inside the warp, the box halo for lanes 0 and 31
+        T eu = T(0), ev = T(0);
+        if (lane_w || lane_e) { eu = pu_[eoff]; ev = pv_[eoff]; }
+        const T su = __shfl_up_sync(0xffffffffu, a0.a[N - 1], 1), sd = __shfl_down_sync(0xffffffffu, a0.a[0], 1);
+        const T tu = __shfl_up_sync(0xffffffffu, b0.a[N - 1], 1), td = __shfl_down_sync(0xffffffffu, b0.a[0], 1);
+        const T uw = lane_w ? eu : su, ue = lane_e ? eu : sd;
+        const T vw = lane_w ? ev : tu, ve = lane_e ? ev : td;
+        if (vec_active) {
+            Vec<T> ou, ov;
+            update_vec<T, ARITH, NOISE>(am, a0, ap, us, un, uw, ue, bm, b0, bp, vs, vn, vw, ve, p, x, y, z, ou, ov);
+            store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
+            pou += pxy;
+            pov += pxy;
+        }
+    }
+}
+
+template <typename T, int ARITH, bool NOISE, int TY, int STAGES, int MINB>
+__global__ void __launch_bounds__(32 * (TY + 1), MINB)
 stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_v,
                    T* __restrict__ uo, T* __restrict__ vo, const Layout L, const Params p, const Box box,
                    const int zchunk) {
     using Tile = TmaTile<T, TY>;
     constexpr int N = Tile::N;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    // carve: [stages][2 fields][FIELD_BYTES] | full[STAGES] | empty[STAGES]
-    unsigned char* tiles = (unsigned char*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
-    unsigned long long* bars = (unsigned long long*)(tiles + (size_t)STAGES * Tile::STAGE_BYTES);
-    const unsigned bar0 = smem_u32(bars);
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    // carve: [stages][2 fields][FIELD_BYTES] | full[STAGES] | empty[STAGES]; keep the shared address
+    // space visible to the compiler (LDS, not generic LD): offset the array, do not round a pointer
+    const unsigned pad = (128u - (smem_u32(smem_raw) & 127u)) & 127u;
+    unsigned char* tiles = smem_raw + pad;
+    const unsigned tiles_u32 = smem_u32(tiles);
+    const unsigned bar0 = tiles_u32 + (unsigned)(STAGES * Tile::STAGE_BYTES);
     auto full_bar = [&](int s) { return bar0 + 8u * (unsigned)s; };
     auto empty_bar = [&](int s) { return bar0 + 8u * (unsigned)(STAGES + s); };
 
@@ -209,14 +249,16 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
         if (lane == 0) {
             const int c0 = L.xoff + xtile - N;           // element index in row
             const int c1 = ytile;                        // row index of y = ytile-1
+            int s = 0;
+            unsigned ph = 1;                             // fresh barriers: waiting on parity 1 passes
             for (int i = 0; i < nplanes; ++i) {
-                const int s = i % STAGES;
-                mbar_wait(empty_bar(s), ((i / STAGES) & 1) ^ 1);
+                mbar_wait(empty_bar(s), ph);
                 mbar_expect_tx(full_bar(s), 2u * (unsigned)Tile::BOX_BYTES);
-                const unsigned dst = smem_u32(tiles + (size_t)s * Tile::STAGE_BYTES);
+                const unsigned dst = tiles_u32 + (unsigned)(s * Tile::STAGE_BYTES);
                 const int c2 = zs + i;                   // plane index of z = zs-1+i
                 tma_load_3d(dst, &map_u, c0, c1, c2, full_bar(s));
                 tma_load_3d(dst + Tile::FIELD_BYTES, &map_v, c0, c1, c2, full_bar(s));
+                if (++s == STAGES) { s = 0; ph ^= 1u; }
             }
         }
         return;
@@ -230,46 +272,42 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
     const long long out0 = vec_active ? L.idx(x, y, zs) : 0;
     T* pou = uo + out0;
     T* pov = vo + out0;
+    const int roff = (w + 1) * Tile::BW + N + lane * N;  // my centre vector in the box (elements)
+    const bool lane_w = lane == 0, lane_e = lane == 31;
+    const int eoff = lane_w ? roff - 1 : roff + N;       // the halo scalar an edge lane needs
 
-    Vec<T> um, u0, up, vm, v0, vp;
+    Vec<T> ua, ub, uc, va, vb, vc;
 #pragma unroll
-    for (int i = 0; i < N; ++i) { um.a[i] = u0.a[i] = up.a[i] = vm.a[i] = v0.a[i] = vp.a[i] = T(0); }
+    for (int q = 0; q < N; ++q) { ua.a[q] = ub.a[q] = uc.a[q] = va.a[q] = vb.a[q] = vc.a[q] = T(0); }
 
-    for (int i = 0; i < nplanes; ++i) {
-        const int s = i % STAGES;
-        mbar_wait(full_bar(s), (i / STAGES) & 1);
-        const T* su_ = (const T*)(tiles + (size_t)s * Tile::STAGE_BYTES);
-        const T* sv_ = (const T*)(tiles + (size_t)s * Tile::STAGE_BYTES + Tile::FIELD_BYTES);
-        const int roff = (w + 1) * Tile::BW + N + lane * N;     // my centre vector in the box
-        up = ld_vec(su_ + roff);
-        vp = ld_vec(sv_ + roff);
-        if (i >= 2) {
-            const int sp = (i - 1) % STAGES;                      // slot holding plane z
-            const T* pu_ = (const T*)(tiles + (size_t)sp * Tile::STAGE_BYTES);
-            const T* pv_ = (const T*)(tiles + (size_t)sp * Tile::STAGE_BYTES + Tile::FIELD_BYTES);
-            const Vec<T> us = ld_vec(pu_ + roff - Tile::BW), un = ld_vec(pu_ + roff + Tile::BW);
-            const Vec<T> vs = ld_vec(pv_ + roff - Tile::BW), vn = ld_vec(pv_ + roff + Tile::BW);
-            T uw = __shfl_up_sync(0xffffffffu, u0.a[N - 1], 1);
-            T ue = __shfl_down_sync(0xffffffffu, u0.a[0], 1);
-            T vw = __shfl_up_sync(0xffffffffu, v0.a[N - 1], 1);
-            T ve = __shfl_down_sync(0xffffffffu, v0.a[0], 1);
-            if (lane == 0) { uw = pu_[roff - 1]; vw = pv_[roff - 1]; }
-            if (lane == 31) { ue = pu_[roff + N]; ve = pv_[roff + N]; }
-            if (vec_active) {
-                const int z = zs + i - 2;
-                Vec<T> ou, ov;
-                update_vec<T, ARITH, NOISE>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, x, y, z, ou, ov);
-                store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
-                pou += L.pxy; pov += L.pxy;
-            }
-        }
-        if (i >= 1) {
-            __syncwarp();
-            if (lane == 0) mbar_arrive(empty_bar((i - 1) % STAGES));
-        }
-        um = u0; u0 = up;
-        vm = v0; v0 = vp;
+    int s = 0, sprev = 0;
+    unsigned ph = 0;
+    // one step of the ring: wait for plane i, consume, release the slot of plane i-1
+#define GSB_TMA_STEP(AM, A0, AP, BM, B0, BP)                                                              \
+    {                                                                                                     \
+        mbar_wait(full_bar(s), ph);                                                                       \
+        tma_consume<T, ARITH, NOISE, TY>(tiles + s * Tile::STAGE_BYTES, tiles + sprev * Tile::STAGE_BYTES, i, \
+                                         AM, A0, AP, BM, B0, BP, roff, eoff, lane_w, lane_e, vec_active, p, box, x, \
+                                         y, zs + i - 2, pou, pov, L.pxy);                                \
+        if (i >= 1) {                                                                                     \
+            __syncwarp();                                                                                 \
+            if (lane == 0) mbar_arrive(empty_bar(sprev));                                                 \
+        }                                                                                                 \
+        sprev = s;                                                                                        \
+        if (++s == STAGES) { s = 0; ph ^= 1u; }                                                           \
+        ++i;                                                                                              \
     }
+    int i = 0;
+    while (i + 3 <= nplanes) {
+        GSB_TMA_STEP(ua, ub, uc, va, vb, vc)
+        GSB_TMA_STEP(ub, uc, ua, vb, vc, va)
+        GSB_TMA_STEP(uc, ua, ub, vc, va, vb)
+    }
+    if (i < nplanes) {
+        GSB_TMA_STEP(ua, ub, uc, va, vb, vc)
+        if (i < nplanes) GSB_TMA_STEP(ub, uc, ua, vb, vc, va)
+    }
+#undef GSB_TMA_STEP
 }
 
 // ------------------------------------------------------------------------------------------

@@ -44,7 +44,8 @@ int main(int argc, char** argv) {
     for (const std::string& v : variants) {
         char kind[16]; int ty = 0, sg = 0, zc = 0;
         if (sscanf(v.c_str(), "%15[^:]:%d:%d:%d", kind, &ty, &sg, &zc) < 2) { fprintf(stderr, "bad variant %s\n", v.c_str()); continue; }
-        if (gsb_set_kernel(h, !strcmp(kind, "l1") ? GSB_KERNEL_L1 : GSB_KERNEL_TMA, ty, sg, zc)) {
+        const int kk = !strcmp(kind, "l1") ? GSB_KERNEL_L1 : !strcmp(kind, "tmalo") ? GSB_KERNEL_TMA_LO : !strcmp(kind, "tmahi") ? GSB_KERNEL_TMA_HI : GSB_KERNEL_TMA;
+        if (gsb_set_kernel(h, kk, ty, sg, zc)) {
             printf("%-16s skipped: %s\n", v.c_str(), gsb_last_error());
             continue;
         }

@@ -4,6 +4,7 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -132,6 +133,10 @@ static Params make_params(const gsb_handle* h) {
         p.fdt = (float)c.dt; p.fnoise = (float)c.noise;
         p.dt_is_one = c.dt == 1.0;
     }
+    p.noise_s = ldexp(p.noise, -31);
+    p.noise_fast = p.noise == 0.0 || (std::isnormal(p.noise_s) && ldexp(p.noise_s, 31) == p.noise);
+    p.fDu6 = p.fDu / 6.0f;
+    p.fDv6 = p.fDv / 6.0f;
     p.seed_lo = (unsigned)(c.seed & 0xffffffffu);
     p.seed_hi = (unsigned)(c.seed >> 32);
     p.step = (unsigned)h->step;
@@ -140,7 +145,7 @@ static Params make_params(const gsb_handle* h) {
 }
 
 static int ensure_maps(gsb_handle* h) {
-    if (h->kcfg.kind != KERNEL_TMA) return 0;
+    if (h->kcfg.kind == KERNEL_L1) return 0;
     if (h->map_ty == h->kcfg.ty) return 0;
     for (int i = 0; i < 4; ++i) {
         const char* err = nullptr;
@@ -160,9 +165,29 @@ static void swap_bindings(gsb_handle* h) {
 }
 
 static bool kernel_shape_ok(const StencilCfg& k) {
-    return k.kind == KERNEL_TMA
-               ? ((k.ty == 8 && (k.stages == 4 || k.stages == 6)) || (k.ty == 16 && (k.stages == 3 || k.stages == 4)))
+    return k.kind != KERNEL_L1
+               ? ((k.ty == 4 && (k.stages == 4 || k.stages == 8)) || (k.ty == 8 && (k.stages == 3 || k.stages == 4 || k.stages == 6)) ||
+                  (k.ty == 16 && (k.stages == 3 || k.stages == 4)))
                : (k.ty == 4 || k.ty == 8);
+}
+
+// Measured best shapes on B200 (profiles/r1_tuning.md): occupancy class, rows per CTA, ring depth,
+// planes per CTA; small grids get shorter z chunks so that every SM still holds several CTAs.
+static void default_kernel(gsb_handle* h) {
+    StencilCfg& k = h->kcfg;
+    const bool nz = k.noise != 0;
+    if (k.dtype == DT_F64) {
+        k.kind = KERNEL_TMA_LO; k.ty = 8;
+        if (nz) { k.stages = 4; k.zchunk = 64; } else { k.stages = 6; k.zchunk = 32; }
+    } else if (k.arith == ARITH_NATIVE) {
+        k.kind = KERNEL_TMA_HI; k.ty = 8;
+        if (nz) { k.stages = 6; k.zchunk = 32; } else { k.stages = 4; k.zchunk = 16; }
+    } else {
+        k.kind = KERNEL_TMA_HI; k.ty = 8; k.stages = 4; k.zchunk = 64;
+    }
+    const int n = (int)(16 / h->es);
+    const long long tiles = (long long)((h->L.sx + 32 * n - 1) / (32 * n)) * ((h->L.sy + k.ty - 1) / k.ty);
+    while (k.zchunk > 8 && tiles * ((h->L.sz + k.zchunk - 1) / k.zchunk) < 148 * 8) k.zchunk /= 2;
 }
 
 static int parse_kernel_env(StencilCfg* k) {
@@ -173,6 +198,8 @@ static int parse_kernel_env(StencilCfg* k) {
     const int n = sscanf(e, "%15[^:]:%d:%d:%d", kind, &ty, &st, &zc);
     if (n < 1) return fail("GSB_KERNEL: expected kind:ty:stages:zchunk, got '%s'", e);
     if (!strcmp(kind, "tma")) k->kind = KERNEL_TMA;
+    else if (!strcmp(kind, "tmalo")) k->kind = KERNEL_TMA_LO;
+    else if (!strcmp(kind, "tmahi")) k->kind = KERNEL_TMA_HI;
     else if (!strcmp(kind, "l1")) k->kind = KERNEL_L1;
     else return fail("GSB_KERNEL: unknown kind '%s' (tma|l1)", kind);
     if (n >= 2 && ty > 0) k->ty = ty;
@@ -295,7 +322,7 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
     CK(cudaMalloc(&h->stats_partials, sizeof(double) * (size_t)stats_scratch_doubles()));
     CK(cudaMalloc(&h->stats_out, sizeof(double) * 5));
     h->kcfg.dtype = c.dtype; h->kcfg.arith = c.arith; h->kcfg.noise = c.noise != 0.0;
-    h->kcfg.kind = KERNEL_TMA; h->kcfg.ty = 8; h->kcfg.stages = 4; h->kcfg.zchunk = 64;
+    default_kernel(h);
     if (parse_kernel_env(&h->kcfg)) return 1;
     return ensure_maps(h);
 }
@@ -420,7 +447,7 @@ extern "C" int gsb_field_stats(gsb_t* h, int which, double thresh, double out[5]
 extern "C" int gsb_set_kernel(gsb_t* h, int kind, int ty, int stages, int zchunk) {
     if (!h) return fail("null handle");
     StencilCfg k = h->kcfg;
-    if (kind == GSB_KERNEL_TMA || kind == GSB_KERNEL_L1) k.kind = kind;
+    if (kind >= GSB_KERNEL_TMA && kind <= GSB_KERNEL_TMA_HI) k.kind = kind;
     else if (kind >= 0) return fail("unknown kernel kind %d", kind);
     if (ty > 0) k.ty = ty;
     if (stages > 0) k.stages = stages;

@@ -44,8 +44,10 @@ extern "C" {
 #define GSB_ARITH_NATIVE 1
 
 /* stencil kernel variants (gsb_set_kernel) */
-#define GSB_KERNEL_TMA 0
-#define GSB_KERNEL_L1 1
+#define GSB_KERNEL_TMA 0    /* TMA-staged tiles, occupancy chosen per arithmetic */
+#define GSB_KERNEL_L1 1     /* no shared memory, y neighbours through L1 */
+#define GSB_KERNEL_TMA_LO 2 /* TMA, register cap for the lower occupancy */
+#define GSB_KERNEL_TMA_HI 3 /* TMA, register cap for the higher occupancy */
 
 /* neighbour slots, the order of MPICartDomain.proc_neighbors (communication.jl:90-92) */
 #define GSB_WEST 0  /* x-1 */
