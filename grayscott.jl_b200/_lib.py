@@ -72,6 +72,7 @@ _PROTOS = [
     ("gsb_compute_stream", _i, [_vp, C.POINTER(_vp)]),
     ("gsb_calculate_arrays", _i, [_i, _i, C.POINTER(_i64), C.POINTER(_i64), _vp, _vp, _vp, _vp] +
      [C.c_double] * 6 + [C.c_uint64, C.c_uint32, _vp]),
+    ("gsb_field_stats_noalloc", _i, [_i, C.POINTER(_i64), _vp, C.c_double, _vp, _vp, C.c_char_p, C.c_size_t]),
 ]
 SYMBOLS = [p[0] for p in _PROTOS]
 

@@ -207,6 +207,36 @@ int gsb_calculate_arrays(int dtype, int arith, const int64_t sizes[3], const int
                          double Du, double Dv, double F, double k, double dt, double noise,
                          uint64_t seed, uint32_t step, void* stream);
 
+/* ---- statistics without any allocation --------------------------------------------------- */
+
+/* No counterpart in the reference (it has no on-device reductions; its analysis script works on
+ * the files ADIOS2 wrote).
+ *
+ * Same five numbers as gsb_field_stats -- sum, sum of squares, min, max, count(value > thresh)
+ * over the interior cells -- but for a caller that may not allocate device memory: a host whose
+ * GPU memory is owned end to end by another allocator (CUDA.jl's pool, PyTorch's caching
+ * allocator), where a cudaMalloc from inside this library can fail or fragment although the pool
+ * has room, or an in-situ hook inside the time loop, where cudaMalloc/cudaFree could synchronise
+ * the device and stall the overlapped halo exchange.  No handle is needed (gsb_create allocates).
+ *
+ *   field_dev : DEVICE array in the reference layout, ghosted: (sx+2)(sy+2)(sz+2), x fastest
+ *   out_dev   : 5 doubles the GPU can write (device or pinned host memory), caller-owned
+ *   stream    : a cudaStream_t or NULL; the call only enqueues two kernels
+ *   errbuf    : optional; receives the reason when the result is non-zero
+ *
+ * The per-plane partial results go to a fixed array inside the library image (160 KiB of device
+ * memory on every GPU that loads the library, held until exit), so:
+ *   - sizes[2] (z-planes) must be <= GSB_NOALLOC_MAX_PLANES, larger fields are refused;
+ *   - calls that overlap on the GPU (different streams, no ordering) race on that array -- keep
+ *     them on one stream or order them with events; back-to-back calls on one stream are fine
+ *     and need no clearing in between (every slot that is read is written first, each call);
+ *   - the FIRST call on each device resolves the array's device address and should therefore be
+ *     made before any stream capture begins on that device.
+ * It calls no cudaMalloc / cudaFree / allocating library routine. */
+#define GSB_NOALLOC_MAX_PLANES 4096
+int gsb_field_stats_noalloc(int dtype, const int64_t sizes[3], const void* field_dev, double thresh,
+                            double* out_dev, void* stream, char* errbuf, size_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif
