@@ -330,7 +330,7 @@ def run_b200(a):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": float(a.L) ** 3 * bpc,
-                "kernel": f"stencil_{'tma' if kern[0].value == 0 else 'l1'}_kernel ty={kern[1].value} stages={kern[2].value} zchunk={kern[3].value}",
+                "kernel": f"stencil_{'l1' if kern[0].value == 1 else 'tma'}_kernel ty={kern[1].value} stages={kern[2].value} zchunk={kern[3].value}",
                 "note": ("per-GPU algorithmic bytes / per-step device time" +
                          ("" if world == 1 else "; at N>1 the step also holds pack/unpack, NCCL and shell launches"))}
     line = {

@@ -67,5 +67,45 @@ int main(int argc, char** argv) {
         fflush(stdout);
     }
     OK(gsb_destroy(h));
+
+    // GS_TUNE_RANKS=n: n weak-scaled subdomains (L^3 each, the reference decomposition) as in-process
+    // ranks on this one device; isolates the cost of the interior/shell split and of pack/unpack
+    // from the transport.  Ideal time per step = n x the single-subdomain time.
+    const char* er = getenv("GS_TUNE_RANKS");
+    const int nr = er ? atoi(er) : 0;
+    if (nr > 1) {
+        std::vector<gsb_t*> hs(nr, nullptr);
+        int32_t dims[3];
+        OK(gsb_dims_create(nr, dims));
+        for (int r = 0; r < nr; ++r) {
+            gsb_config c = cfg;
+            OK(gsb_fill_domain(&c, L * dims[0], nr, r));
+            for (int d = 0; d < 3; ++d) { c.global[d] = L * dims[d]; c.sizes[d] = L; c.offsets[d] = L * c.coords[d]; }
+            c.dtype = dtype; c.arith = arith; c.Du = cfg.Du; c.Dv = cfg.Dv; c.F = cfg.F; c.k = cfg.k; c.dt = cfg.dt;
+            c.noise = noise; c.seed = cfg.seed; c.device = 0;
+            OK(gsb_create(&hs[r], &c));
+            OK(gsb_init_fields(hs[r]));
+        }
+        OK(gsb_comm_init_local(hs.data(), nr));
+        void* sv0 = nullptr;
+        OK(gsb_compute_stream(hs[nr - 1], &sv0));
+        OK(gsb_step_group(hs.data(), nr, 3));
+        for (int r = 0; r < nr; ++r) OK(gsb_sync(hs[r]));
+        OK(gsb_timers_enable(hs[0], 1));
+        cudaEventRecord(e0, 0);
+        cudaDeviceSynchronize();
+        cudaEventRecord(e0, 0);
+        OK(gsb_step_group(hs.data(), nr, steps));
+        for (int r = 0; r < nr; ++r) OK(gsb_sync(hs[r]));
+        cudaEventRecord(e1, 0);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double t[4];
+        OK(gsb_timers(hs[0], t));
+        printf("ranks=%d on one device: %8.4f ms/step total = %8.4f ms per subdomain; rank0 last step: halo %.3f interior %.3f shell %.3f step %.3f ms\n",
+               nr, ms / steps, ms / steps / nr, t[0], t[1], t[2], t[3]);
+        for (int r = 0; r < nr; ++r) OK(gsb_destroy(hs[r]));
+    }
     return 0;
 }

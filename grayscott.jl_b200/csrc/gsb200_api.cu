@@ -302,8 +302,12 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
     h->L = make_layout((int)c.sizes[0], (int)c.sizes[1], (int)c.sizes[2], h->es);
     const size_t bytes = (size_t)h->L.elems() * h->es;
     for (int i = 0; i < 4; ++i) CK(cudaMalloc(&h->f[i], bytes));
-    CK(cudaStreamCreateWithFlags(&h->s_compute, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&h->s_comm, cudaStreamNonBlocking));
+    // the halo path (pack, NCCL, unpack) must not queue behind the thousands of CTAs of the interior
+    // update: highest priority for the communication stream, lowest for the update stream
+    int prio_lo = 0, prio_hi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CK(cudaStreamCreateWithPriority(&h->s_compute, cudaStreamNonBlocking, prio_lo));
+    CK(cudaStreamCreateWithPriority(&h->s_comm, cudaStreamNonBlocking, prio_hi));
     CK(cudaEventCreateWithFlags(&h->ev_compute, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_halo, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_packed, cudaEventDisableTiming));
@@ -478,7 +482,7 @@ extern "C" int gsb_timers(gsb_t* h, double out_ms[4]) {
     float a = 0, b = 0, c = 0, d = 0;
     if (h->n_active) CK(cudaEventElapsedTime(&a, h->tev[0], h->tev[1]));
     CK(cudaEventElapsedTime(&b, h->tev[2], h->tev[3]));
-    CK(cudaEventElapsedTime(&c, h->tev[3], h->tev[4]));
+    CK(cudaEventElapsedTime(&c, h->tev[5], h->tev[4]));   // shell kernels only, after the halo arrived
     CK(cudaEventElapsedTime(&d, h->tev[2], h->tev[4]));
     out_ms[0] = a; out_ms[1] = b; out_ms[2] = c; out_ms[3] = d;
     return 0;
@@ -658,12 +662,13 @@ static int enqueue_compute_overlapped(gsb_handle* h) {
     const bool split = h->n_active > 0 && interior_box(h, &in);
     if (!split) {
         if (h->n_active) CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
-        if (h->timers_on) CK(cudaEventRecord(h->tev[3], h->s_compute));
+        if (h->timers_on) { CK(cudaEventRecord(h->tev[3], h->s_compute)); CK(cudaEventRecord(h->tev[5], h->s_compute)); }
         if (launch_box(h, full_box(h), p)) return 1;
     } else {
         if (launch_box(h, in, p)) return 1;
         if (h->timers_on) CK(cudaEventRecord(h->tev[3], h->s_compute));
         CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+        if (h->timers_on) CK(cudaEventRecord(h->tev[5], h->s_compute));
         const int sx = h->L.sx, sy = h->L.sy, sz = h->L.sz;
         // disjoint slabs: z slabs span everything, y slabs the interior z range, x slabs the interior y,z range
         if (in.z0 > 0) if (launch_box(h, Box{0, sx, 0, sy, 0, in.z0}, p)) return 1;

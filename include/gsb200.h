@@ -180,7 +180,8 @@ int gsb_set_kernel(gsb_t* h, int kind, int ty, int stages, int zchunk);
 int gsb_get_kernel(gsb_t* h, int* kind, int* ty, int* stages, int* zchunk);
 
 /* Per-phase device times of the LAST step enqueued by gsb_step (ms): out[0] = halo (pack,
- * transport, unpack), out[1] = interior update, out[2] = shell update, out[3] = whole step.
+ * transport, unpack), out[1] = interior update, out[2] = shell update (after the halo
+ * arrived), out[3] = whole step.
  * Enable before stepping; synchronises when read. */
 int gsb_timers_enable(gsb_t* h, int on);
 int gsb_timers(gsb_t* h, double out_ms[4]);
