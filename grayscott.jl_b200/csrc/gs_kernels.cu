@@ -113,18 +113,26 @@ long long face_elems(const Layout& L, int dir) {
     }
 }
 
-// element e of face `dir` -> interior coordinates; `ghost` selects the ghost layer (unpack) or the
-// boundary interior layer (pack)
-__device__ __forceinline__ long long face_index(const Layout& L, int dir, long long e, bool ghost) {
+long long face_piece_elems(const Layout& L, int dir, int z0, int z1) {
+    switch (dir >> 1) {
+        case 0: return (long long)L.sy * (z1 - z0);
+        case 1: return (long long)L.sx * (z1 - z0);
+        default: return (long long)L.sx * L.sy;
+    }
+}
+
+// element e of the piece of face `dir` that starts at plane zb -> interior coordinates; `ghost`
+// selects the ghost layer (unpack) or the boundary interior layer (pack)
+__device__ __forceinline__ long long face_index(const Layout& L, int dir, long long e, int zb, bool ghost) {
     int x, y, z;
     const bool hi = dir & 1;
     switch (dir >> 1) {
         case 0:
-            y = (int)(e % L.sy); z = (int)(e / L.sy);
+            y = (int)(e % L.sy); z = zb + (int)(e / L.sy);
             x = hi ? (ghost ? L.sx : L.sx - 1) : (ghost ? -1 : 0);
             break;
         case 1:
-            x = (int)(e % L.sx); z = (int)(e / L.sx);
+            x = (int)(e % L.sx); z = zb + (int)(e / L.sx);
             y = hi ? (ghost ? L.sy : L.sy - 1) : (ghost ? -1 : 0);
             break;
         default:
@@ -140,6 +148,7 @@ struct FaceArgs {
     int dir[6];
     void* buf[6];
     long long count[6];
+    int zb[6];
 };
 
 template <typename T, bool PACK>
@@ -148,10 +157,11 @@ __global__ void faces_kernel(T* __restrict__ u, T* __restrict__ v, Layout L, Fac
     if (f >= fa.n) return;
     const int dir = fa.dir[f];
     const long long n = fa.count[f];
+    const int zb = fa.zb[f];
     T* buf = (T*)fa.buf[f];
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += stride) {
-        const long long i = face_index(L, dir, e, !PACK);
+        const long long i = face_index(L, dir, e, zb, !PACK);
         if (PACK) { buf[e] = u[i]; buf[n + e] = v[i]; }
         else { u[i] = buf[e]; v[i] = buf[n + e]; }
     }
@@ -163,9 +173,10 @@ static cudaError_t faces_launch(int dtype, void* u, void* v, const Layout& L, co
     FaceArgs fa;
     fa.n = fs.n;
     long long maxn = 0;
-    for (int i = 0; i < 6; ++i) { fa.dir[i] = 0; fa.buf[i] = nullptr; fa.count[i] = 0; }
+    for (int i = 0; i < 6; ++i) { fa.dir[i] = 0; fa.buf[i] = nullptr; fa.count[i] = 0; fa.zb[i] = 0; }
     for (int i = 0; i < fs.n; ++i) {
-        fa.dir[i] = fs.dir[i]; fa.buf[i] = fs.buf[i]; fa.count[i] = face_elems(L, fs.dir[i]);
+        fa.dir[i] = fs.dir[i]; fa.buf[i] = fs.buf[i]; fa.zb[i] = fs.z0[i];
+        fa.count[i] = face_piece_elems(L, fs.dir[i], fs.z0[i], fs.z1[i]);
         if (fa.count[i] > maxn) maxn = fa.count[i];
     }
     if (maxn == 0) return cudaSuccess;

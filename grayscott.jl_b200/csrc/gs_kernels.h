@@ -46,9 +46,12 @@ cudaError_t launch_init_fields(int dtype, void* u, void* v, void* ut, void* vt, 
 struct FaceSet {
     int n;            // number of faces in this launch (<= 6)
     int dir[6];
-    void* buf[6];     // message buffer per face
+    void* buf[6];     // message buffer per face (piece)
+    int z0[6], z1[6]; // x and y faces: the z range [z0, z1) this piece covers (z faces: ignored)
 };
 long long face_elems(const Layout& L, int dir);
+// elements of the piece of face `dir` restricted to planes [z0, z1) (z faces: the whole plane)
+long long face_piece_elems(const Layout& L, int dir, int z0, int z1);
 // pack: boundary interior cells of (u, v) -> buf ; unpack: buf -> ghost cells of (u, v)
 cudaError_t launch_pack_faces(int dtype, const void* u, const void* v, const Layout& L, const FaceSet& fs,
                               cudaStream_t st);

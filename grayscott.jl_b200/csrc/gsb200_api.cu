@@ -82,6 +82,8 @@ static int nccl_load() {
 
 // ------------------------------------------------------------------ handle
 enum : int { TR_NONE = 0, TR_LOCAL = 1, TR_NCCL = 2 };
+enum : int { HALO_PIPELINE = 0, HALO_SPLIT = 1 };
+#define GSB_MAX_CHUNKS 16
 
 struct gsb_handle {
     gsb_config cfg;
@@ -93,7 +95,10 @@ struct gsb_handle {
     CUtensorMap map[4];     // tensor map of f[i] for the current TMA tile height
     int map_ty;             // tile height the maps were encoded for (0 = none)
     cudaStream_t s_compute, s_comm;
-    cudaEvent_t ev_compute, ev_halo, ev_packed;
+    cudaEvent_t ev_compute, ev_halo, ev_packed, ev_chunk;
+    cudaEvent_t ev_piece[GSB_MAX_CHUNKS];   // pipelined halo: piece k of the previous step has landed
+    int halo_mode, halo_chunks;
+    bool ghost_valid;       // the ghosts of the current fields already hold the neighbours' current values
     long long step;
     StencilCfg kcfg;
     // halo
@@ -271,6 +276,8 @@ extern "C" int gsb_destroy(gsb_t* h) {
     if (h->ev_compute) cudaEventDestroy(h->ev_compute);
     if (h->ev_halo) cudaEventDestroy(h->ev_halo);
     if (h->ev_packed) cudaEventDestroy(h->ev_packed);
+    if (h->ev_chunk) cudaEventDestroy(h->ev_chunk);
+    for (int k = 0; k < GSB_MAX_CHUNKS; ++k) if (h->ev_piece[k]) cudaEventDestroy(h->ev_piece[k]);
     for (int i = 0; i < 6; ++i) if (h->tev[i]) cudaEventDestroy(h->tev[i]);
     delete h;
     return 0;
@@ -311,6 +318,14 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
     CK(cudaEventCreateWithFlags(&h->ev_compute, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_halo, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_packed, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_chunk, cudaEventDisableTiming));
+    for (int k = 0; k < GSB_MAX_CHUNKS; ++k) CK(cudaEventCreateWithFlags(&h->ev_piece[k], cudaEventDisableTiming));
+    {
+        const char* hm = getenv("GSB_HALO");          // pipeline (default) | split
+        h->halo_mode = (hm && !strcmp(hm, "split")) ? HALO_SPLIT : HALO_PIPELINE;
+        const char* hc = getenv("GSB_HALO_CHUNKS");
+        h->halo_chunks = hc ? atoi(hc) : 0;
+    }
     for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&h->tev[i]));
     h->n_active = 0;
     for (int d = 0; d < 6; ++d) {
@@ -351,10 +366,12 @@ extern "C" int gsb_init_fields(gsb_t* h) {
     if (!h) return fail("null handle");
     CK(cudaSetDevice(h->device));
     const long long off[3] = {h->cfg.offsets[0], h->cfg.offsets[1], h->cfg.offsets[2]};
-    CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+    CK(cudaStreamSynchronize(h->s_comm));      // no halo piece may still be landing in the ghosts
+    CK(cudaStreamSynchronize(h->s_compute));
     CK(launch_init_fields(h->cfg.dtype, h->f[0], h->f[1], h->f[2], h->f[3], h->L, h->global, off, h->s_compute));
     CK(cudaEventRecord(h->ev_compute, h->s_compute));
     h->step = 0;
+    h->ghost_valid = false;
     return 0;
 }
 
@@ -410,6 +427,7 @@ extern "C" int gsb_set_ghosted(gsb_t* h, int which, const void* host) {
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->s_comm));
     if (copy_field(h, h->f[which], const_cast<void*>(host), 1, false)) return 1;
+    h->ghost_valid = false;
     CK(cudaEventRecord(h->ev_compute, h->s_compute));
     CK(cudaStreamSynchronize(h->s_compute));
     return 0;
@@ -593,30 +611,55 @@ static bool interior_box(const gsb_handle* h, Box* b) {
     return true;
 }
 
-// pack -> (transport) : first half of exchange!, on the comm stream
-static int enqueue_pack_send(gsb_handle* h) {
+// A piece of the halo: which faces travel, and for the x / y faces which z range.
+struct Piece {
+    int z0, z1;
+    bool send[6], recv[6];
+};
+
+static Piece whole_piece(const gsb_handle* h) {
+    Piece p;
+    p.z0 = 0; p.z1 = h->L.sz;
+    for (int d = 0; d < 6; ++d) p.send[d] = p.recv[d] = h->active[d];
+    return p;
+}
+
+// byte offset of a piece inside the message buffer of face d ([u piece | v piece], pieces in z order)
+static size_t piece_offset(const gsb_handle* h, int d, int z0) {
+    if ((d >> 1) == 2) return 0;
+    const long long row = (d >> 1) == 0 ? h->L.sy : h->L.sx;
+    return (size_t)(2 * row * z0) * h->es;
+}
+
+// pack -> (transport): first half of an exchange, on the communication stream.
+//   src = 0: the fields as bound now (u, v); src = 1: the fields being written (u_temp, v_temp)
+//   par: which of the two receive buffers this exchange uses
+static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, cudaEvent_t after) {
     CK(cudaSetDevice(h->device));
-    CK(cudaStreamWaitEvent(h->s_comm, h->ev_compute, 0));       // current fields are final
+    CK(cudaStreamWaitEvent(h->s_comm, after, 0));               // the cells to send are final
     if (h->timers_on) CK(cudaEventRecord(h->tev[0], h->s_comm));
-    const int par = (int)(h->step & 1);
     FaceSet fs;
     fs.n = 0;
     for (int d = 0; d < 6; ++d) {
-        if (!h->active[d]) continue;
+        if (!pc.send[d]) continue;
+        char* base = (char*)(h->transport == TR_LOCAL ? h->peer[d]->recv[par][opp(d)] : h->send[d]);
         fs.dir[fs.n] = d;
-        fs.buf[fs.n] = h->transport == TR_LOCAL ? h->peer[d]->recv[par][opp(d)] : h->send[d];
+        fs.buf[fs.n] = base + piece_offset(h, d, pc.z0);
+        fs.z0[fs.n] = pc.z0; fs.z1[fs.n] = pc.z1;
         fs.n++;
     }
-    CK(launch_pack_faces(h->cfg.dtype, h->f[0], h->f[1], h->L, fs, h->s_comm));
-    h->launches += 1;
+    if (fs.n) {
+        CK(launch_pack_faces(h->cfg.dtype, h->f[2 * src], h->f[2 * src + 1], h->L, fs, h->s_comm));
+        h->launches += 1;
+    }
     if (h->transport == TR_NCCL) {
         const ncclDataType_t ty = h->cfg.dtype == GSB_F32 ? ncclFloat : ncclDouble;
         NK(g_nccl.GroupStart());
         for (int d = 0; d < 6; ++d) {
-            if (!h->active[d]) continue;
-            const size_t cnt = 2 * (size_t)face_elems(h->L, d);
-            NK(g_nccl.Send(h->send[d], cnt, ty, h->cfg.neighbors[d], h->comm, h->s_comm));
-            NK(g_nccl.Recv(h->recv[par][d], cnt, ty, h->cfg.neighbors[d], h->comm, h->s_comm));
+            const size_t cnt = 2 * (size_t)face_piece_elems(h->L, d, pc.z0, pc.z1);
+            const size_t off = piece_offset(h, d, pc.z0);
+            if (pc.send[d]) NK(g_nccl.Send((char*)h->send[d] + off, cnt, ty, h->cfg.neighbors[d], h->comm, h->s_comm));
+            if (pc.recv[d]) NK(g_nccl.Recv((char*)h->recv[par][d] + off, cnt, ty, h->cfg.neighbors[d], h->comm, h->s_comm));
         }
         NK(g_nccl.GroupEnd());
     }
@@ -624,25 +667,27 @@ static int enqueue_pack_send(gsb_handle* h) {
     return 0;
 }
 
-// (wait for the neighbours) -> unpack : second half of exchange!
-static int enqueue_unpack(gsb_handle* h) {
+// (wait for the neighbours) -> unpack into the ghosts of the fields `dst` (0: u, v; 1: u_temp, v_temp)
+static int enqueue_unpack(gsb_handle* h, const Piece& pc, int dst, int par, cudaEvent_t done) {
     CK(cudaSetDevice(h->device));
-    const int par = (int)(h->step & 1);
     if (h->transport == TR_LOCAL)
         for (int d = 0; d < 6; ++d)
-            if (h->active[d]) CK(cudaStreamWaitEvent(h->s_comm, h->peer[d]->ev_packed, 0));
+            if (pc.recv[d]) CK(cudaStreamWaitEvent(h->s_comm, h->peer[d]->ev_packed, 0));
     FaceSet fs;
     fs.n = 0;
     for (int d = 0; d < 6; ++d) {
-        if (!h->active[d]) continue;
+        if (!pc.recv[d]) continue;
         fs.dir[fs.n] = d;
-        fs.buf[fs.n] = h->recv[par][d];
+        fs.buf[fs.n] = (char*)h->recv[par][d] + piece_offset(h, d, pc.z0);
+        fs.z0[fs.n] = pc.z0; fs.z1[fs.n] = pc.z1;
         fs.n++;
     }
-    CK(launch_unpack_faces(h->cfg.dtype, h->f[0], h->f[1], h->L, fs, h->s_comm));
-    h->launches += 1;
+    if (fs.n) {
+        CK(launch_unpack_faces(h->cfg.dtype, h->f[2 * dst], h->f[2 * dst + 1], h->L, fs, h->s_comm));
+        h->launches += 1;
+    }
     if (h->timers_on) CK(cudaEventRecord(h->tev[1], h->s_comm));
-    CK(cudaEventRecord(h->ev_halo, h->s_comm));
+    CK(cudaEventRecord(done, h->s_comm));
     return 0;
 }
 
@@ -652,7 +697,7 @@ static int check_transport(gsb_handle* h) {
     return 0;
 }
 
-// interior now, shell after the halo arrived
+// ---- scheme A ("split"): exchange at the start of the step, interior update meanwhile, shell after
 static int enqueue_compute_overlapped(gsb_handle* h) {
     CK(cudaSetDevice(h->device));
     if (ensure_maps(h)) return 1;
@@ -683,13 +728,129 @@ static int enqueue_compute_overlapped(gsb_handle* h) {
     return 0;
 }
 
+// exchange of the current fields, whole faces (exchange! as the reference orders it: before calculate!)
+static int enqueue_exchange_now(gsb_handle* h, bool local_second_half) {
+    const Piece w = whole_piece(h);
+    const int par = (int)(h->step & 1);
+    if (!local_second_half) return enqueue_pack_send(h, w, 0, par, h->ev_compute);
+    return enqueue_unpack(h, w, 0, par, h->ev_halo);
+}
+
+// ---- scheme B ("pipeline", default): the update runs as C launches over z chunks of FULL rows; as
+// soon as a chunk is written, its new boundary values travel to the neighbours and land in the
+// ghosts of the fields being written -- i.e. the exchange! of the NEXT step, one step ahead.  A
+// chunk of the next step waits only for its own piece, which by then is most of a step old.
+static int pipeline_chunks(const gsb_handle* h) {
+    if (!h->n_active) return 1;
+    int c = h->halo_chunks > 0 ? h->halo_chunks : (h->L.sz >= 256 ? 8 : h->L.sz / 32);
+    if (c > GSB_MAX_CHUNKS) c = GSB_MAX_CHUNKS;
+    if (c > h->L.sz) c = h->L.sz;
+    return c < 1 ? 1 : c;
+}
+
+// chunk visiting order: the two chunks that own a z face first, so their planes leave early
+static void chunk_order(int C, int order[GSB_MAX_CHUNKS]) {
+    int n = 0;
+    order[n++] = C - 1;
+    if (C > 1) order[n++] = 0;
+    for (int k = 1; k < C - 1; ++k) order[n++] = k;
+}
+
+static Piece chunk_piece(const gsb_handle* h, int k, int C) {
+    Piece p;
+    p.z0 = (int)((long long)h->L.sz * k / C);
+    p.z1 = (int)((long long)h->L.sz * (k + 1) / C);
+    for (int d = 0; d < 4; ++d) p.send[d] = p.recv[d] = h->active[d];
+    // my lowest plane goes south with chunk 0 and the south neighbour's answer (its highest plane)
+    // comes with ITS last chunk; symmetrically for north
+    p.send[GSB_SOUTH] = h->active[GSB_SOUTH] && k == 0;
+    p.recv[GSB_NORTH] = h->active[GSB_NORTH] && k == 0;
+    p.send[GSB_NORTH] = h->active[GSB_NORTH] && k == C - 1;
+    p.recv[GSB_SOUTH] = h->active[GSB_SOUTH] && k == C - 1;
+    return p;
+}
+
+// which piece event chunk k must see before it may read its ghosts (events complete in visiting order)
+static int chunk_dependency(int k, int C) { return (k == 0 || k == C - 1) ? 0 : k; }
+
+static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, bool first, bool last) {
+    CK(cudaSetDevice(h->device));
+    if (first) {
+        if (ensure_maps(h)) return 1;
+        if (h->timers_on) CK(cudaEventRecord(h->tev[2], h->s_compute));
+    }
+    if (h->n_active) CK(cudaStreamWaitEvent(h->s_compute, h->ev_piece[chunk_dependency(k, C)], 0));
+    const Piece pc = chunk_piece(h, k, C);
+    if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p)) return 1;
+    CK(cudaEventRecord(h->ev_chunk, h->s_compute));
+    if (last) {
+        if (h->timers_on) {
+            CK(cudaEventRecord(h->tev[3], h->s_compute)); CK(cudaEventRecord(h->tev[5], h->s_compute));
+            CK(cudaEventRecord(h->tev[4], h->s_compute));
+            h->timers_valid = true;
+        }
+        CK(cudaEventRecord(h->ev_compute, h->s_compute));
+    }
+    return 0;
+}
+
+// bring the ghosts of the current fields up to date once (first step after init / set / piecewise use)
+static int pipeline_prime(gsb_handle** hs, int n) {
+    bool need = false;
+    for (int r = 0; r < n; ++r) need = need || (hs[r]->n_active && !hs[r]->ghost_valid);
+    if (!need) return 0;
+    for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_exchange_now(hs[r], false)) return 1;
+    for (int r = 0; r < n; ++r) if (hs[r]->n_active) {
+        if (enqueue_exchange_now(hs[r], true)) return 1;
+        for (int k = 0; k < GSB_MAX_CHUNKS; ++k) CK(cudaEventRecord(hs[r]->ev_piece[k], hs[r]->s_comm));
+        hs[r]->ghost_valid = true;
+    }
+    return 0;
+}
+
+static int pipeline_step(gsb_handle** hs, int n) {
+    if (pipeline_prime(hs, n)) return 1;
+    const int C = pipeline_chunks(hs[0]);
+    int order[GSB_MAX_CHUNKS];
+    chunk_order(C, order);
+    Params ps[64];
+    if (n > 64) return fail("too many in-process ranks");
+    for (int r = 0; r < n; ++r) ps[r] = make_params(hs[r]);
+    for (int i = 0; i < C; ++i) {
+        const int k = order[i];
+        for (int r = 0; r < n; ++r) {
+            gsb_handle* h = hs[r];
+            if (pipeline_compute_chunk(h, k, C, ps[r], i == 0, i == C - 1)) return 1;
+            if (h->n_active)
+                if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk)) return 1;
+        }
+        for (int r = 0; r < n; ++r) {
+            gsb_handle* h = hs[r];
+            if (h->n_active)
+                if (enqueue_unpack(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_piece[k])) return 1;
+        }
+    }
+    for (int r = 0; r < n; ++r) { swap_bindings(hs[r]); hs[r]->ghost_valid = hs[r]->n_active > 0; }
+    return 0;
+}
+
+static int split_step(gsb_handle** hs, int n) {
+    for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_exchange_now(hs[r], false)) return 1;
+    for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_exchange_now(hs[r], true)) return 1;
+    for (int r = 0; r < n; ++r) if (enqueue_compute_overlapped(hs[r])) return 1;
+    for (int r = 0; r < n; ++r) { swap_bindings(hs[r]); hs[r]->ghost_valid = false; }
+    return 0;
+}
+
 extern "C" int gsb_exchange(gsb_t* h) {
     if (!h) return fail("null handle");
     if (!h->n_active) return 0;
     if (check_transport(h)) return 1;
     if (h->transport == TR_LOCAL) return fail("gsb_exchange: in-process handles advance together, use gsb_step_group");
-    if (enqueue_pack_send(h)) return 1;
-    return enqueue_unpack(h);
+    if (enqueue_exchange_now(h, false)) return 1;
+    if (enqueue_exchange_now(h, true)) return 1;
+    h->ghost_valid = true;
+    return 0;
 }
 
 extern "C" int gsb_calculate(gsb_t* h) {
@@ -706,6 +867,7 @@ extern "C" int gsb_calculate(gsb_t* h) {
 extern "C" int gsb_swap(gsb_t* h) {
     if (!h) return fail("null handle");
     swap_bindings(h);
+    h->ghost_valid = false;
     return 0;
 }
 
@@ -714,14 +876,8 @@ extern "C" int gsb_step(gsb_t* h, int nsteps) {
     if (nsteps < 0) return fail("nsteps < 0");
     if (check_transport(h)) return 1;
     if (h->transport == TR_LOCAL) return fail("gsb_step: in-process handles advance together, use gsb_step_group");
-    for (int s = 0; s < nsteps; ++s) {
-        if (h->n_active) {
-            if (enqueue_pack_send(h)) return 1;
-            if (enqueue_unpack(h)) return 1;
-        }
-        if (enqueue_compute_overlapped(h)) return 1;
-        swap_bindings(h);
-    }
+    for (int s = 0; s < nsteps; ++s)
+        if (h->halo_mode == HALO_PIPELINE ? pipeline_step(&h, 1) : split_step(&h, 1)) return 1;
     return 0;
 }
 
@@ -733,13 +889,11 @@ extern "C" int gsb_step_group(gsb_t** hs, int n, int nsteps) {
         if (check_transport(hs[r])) return 1;
         if (hs[r]->n_active && hs[r]->transport != TR_LOCAL) return fail("gsb_step_group needs gsb_comm_init_local");
         if (hs[r]->step != hs[0]->step) return fail("handles are at different steps");
+        if (hs[r]->L.sz != hs[0]->L.sz || hs[r]->halo_mode != hs[0]->halo_mode || hs[r]->halo_chunks != hs[0]->halo_chunks)
+            return fail("in-process ranks must share sz and the halo scheme");
     }
-    for (int s = 0; s < nsteps; ++s) {
-        for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_pack_send(hs[r])) return 1;
-        for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_unpack(hs[r])) return 1;
-        for (int r = 0; r < n; ++r) if (enqueue_compute_overlapped(hs[r])) return 1;
-        for (int r = 0; r < n; ++r) swap_bindings(hs[r]);
-    }
+    for (int s = 0; s < nsteps; ++s)
+        if (hs[0]->halo_mode == HALO_PIPELINE ? pipeline_step(hs, n) : split_step(hs, n)) return 1;
     return 0;
 }
 

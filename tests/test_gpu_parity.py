@@ -305,14 +305,25 @@ def test_calculate_arrays_on_caller_device_memory(sim, orc, prec):
 
 
 # ---------------------------------------------------------------- halo exchange (in-process ranks)
+# halo schemes: the default pipelined one (update in z chunks, each chunk's new boundary values sent
+# one step ahead) with several chunk counts, and the interior/shell split
+SCHEMES = [("pipeline", None), ("pipeline", 1), ("pipeline", 2), ("pipeline", 3), ("pipeline", 5), ("split", None)]
+
+
 @pytest.mark.parametrize("prec", ["Float32", "Float64"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
 @pytest.mark.parametrize("noise", [0.0, 0.1])
-def test_halo_exchange_bit_exact_vs_single_subdomain(sim, orc, prec, nranks, noise):
+@pytest.mark.parametrize("scheme", SCHEMES)
+def test_halo_exchange_bit_exact_vs_single_subdomain(sim, orc, monkeypatch, prec, nranks, noise, scheme):
     """N subdomains (the reference's Cartesian decomposition: 2 -> (2,1,1), 4 -> (2,2,1), 8 -> (2,2,2))
     exchanging ghost faces every step == one subdomain of the same global grid, bit for bit, and ==
     the oracle's N-rank run.  The ranks share cuda:0 here; the transport differs from the NCCL one
     only in who moves the packed faces."""
+    monkeypatch.setenv("GSB_HALO", scheme[0])
+    if scheme[1]:
+        monkeypatch.setenv("GSB_HALO_CHUNKS", str(scheme[1]))
+    else:
+        monkeypatch.delenv("GSB_HALO_CHUNKS", raising=False)
     L, steps = 64, 25
     s = settings(sim, L, prec, noise)
     ranks = []
@@ -342,8 +353,12 @@ def test_halo_exchange_bit_exact_vs_single_subdomain(sim, orc, prec, nranks, noi
     one.close()
 
 
-def test_overlap_split_large_enough_to_have_an_interior(sim):
-    """Subdomains big enough that the interior/shell split is active in every direction."""
+@pytest.mark.parametrize("scheme", ["pipeline", "split"])
+def test_overlap_large_subdomains(sim, monkeypatch, scheme):
+    """Subdomains big enough that the interior/shell split is active in every direction and that the
+    pipelined scheme runs its default number of chunks; mixes piecewise calls and iterate!."""
+    monkeypatch.setenv("GSB_HALO", scheme)
+    monkeypatch.delenv("GSB_HALO_CHUNKS", raising=False)
     L, steps, nranks = 320, 6, 8
     s = settings(sim, L, "Float32", 0.1)
     ranks = []
@@ -354,7 +369,9 @@ def test_overlap_split_large_enough_to_have_an_interior(sim):
     ranks[0][1].timers_enable(True)
     sim.iterate_group([f for _, f in ranks], s, nsteps=steps)
     t = ranks[0][1].timers()
-    assert t["shell_ms"] > 0 and t["interior_ms"] > 0 and ranks[0][1].halo_bytes() == 3 * 2 * 160 * 160 * 4
+    assert t["interior_ms"] > 0 and ranks[0][1].halo_bytes() == 3 * 2 * 160 * 160 * 4
+    if scheme == "split":
+        assert t["shell_ms"] > 0
     _, mcd1, one = make(sim, L, "Float32", 0.1, seed=9)
     sim.iterate(one, s, mcd1, nsteps=steps)
     u1, v1 = sim.get_fields(one)
