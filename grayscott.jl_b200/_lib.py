@@ -52,6 +52,8 @@ _PROTOS = [
     ("gsb_step", _i, [_vp, _i]),
     ("gsb_step_group", _i, [C.POINTER(_vp), _i, _i]),
     ("gsb_get_fields", _i, [_vp, _vp, _vp]),
+    ("gsb_get_fields_async", _i, [_vp, _vp, _vp]),
+    ("gsb_output_wait", _i, [_vp]),
     ("gsb_get_ghosted", _i, [_vp, _i, _vp]),
     ("gsb_set_ghosted", _i, [_vp, _i, _vp]),
     ("gsb_alloc_host", _i, [C.POINTER(_vp), C.c_size_t]),

@@ -95,6 +95,14 @@ struct gsb_handle {
     CUtensorMap map[4];     // tensor map of f[i] for the current TMA tile height
     int map_ty;             // tile height the maps were encoded for (0 = none)
     cudaStream_t s_compute, s_comm;
+    cudaStream_t s_compute2;  // pipelined scheme: chunks alternate between two update streams so that the
+                              // next chunk fills the SMs the previous one leaves idle in its tail
+    cudaEvent_t ev_join;
+    // asynchronous output (gsb_get_fields_async): device snapshot + D2H on its own stream
+    cudaStream_t s_copy;
+    cudaEvent_t ev_snap, ev_copied;
+    void* stage[2];          // contiguous ghost-free copies of u and v (allocated on first use)
+    bool copy_in_flight;
     cudaEvent_t ev_compute, ev_halo, ev_packed, ev_chunk;
     cudaEvent_t ev_piece[GSB_MAX_CHUNKS];   // pipelined halo: piece k of the previous step has landed
     int halo_mode, halo_chunks;
@@ -120,6 +128,14 @@ struct gsb_handle {
 };
 
 static inline int opp(int d) { return d ^ 1; }
+
+// timing experiments only ($GSB_DEBUG_SKIP bit 0: no pack kernel, bit 1: no NCCL, bit 2: no unpack kernel):
+// results are wrong when set
+static int debug_skip() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("GSB_DEBUG_SKIP"); v = e ? atoi(e) : 0; }
+    return v;
+}
 
 static Params make_params(const gsb_handle* h) {
     const gsb_config& c = h->cfg;
@@ -273,6 +289,12 @@ extern "C" int gsb_destroy(gsb_t* h) {
     if (h->stats_out) cudaFree(h->stats_out);
     if (h->s_compute) cudaStreamDestroy(h->s_compute);
     if (h->s_comm) cudaStreamDestroy(h->s_comm);
+    if (h->s_compute2) cudaStreamDestroy(h->s_compute2);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->s_copy) cudaStreamDestroy(h->s_copy);
+    if (h->ev_snap) cudaEventDestroy(h->ev_snap);
+    if (h->ev_copied) cudaEventDestroy(h->ev_copied);
+    for (int i = 0; i < 2; ++i) if (h->stage[i]) cudaFree(h->stage[i]);
     if (h->ev_compute) cudaEventDestroy(h->ev_compute);
     if (h->ev_halo) cudaEventDestroy(h->ev_halo);
     if (h->ev_packed) cudaEventDestroy(h->ev_packed);
@@ -315,6 +337,11 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
     CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     CK(cudaStreamCreateWithPriority(&h->s_compute, cudaStreamNonBlocking, prio_lo));
     CK(cudaStreamCreateWithPriority(&h->s_comm, cudaStreamNonBlocking, prio_hi));
+    CK(cudaStreamCreateWithPriority(&h->s_compute2, cudaStreamNonBlocking, prio_lo));
+    CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_snap, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_copied, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_compute, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_halo, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_packed, cudaEventDisableTiming));
@@ -408,6 +435,56 @@ extern "C" int gsb_get_fields(gsb_t* h, void* u_host, void* v_host) {
     if (copy_field(h, h->f[0], u_host, 0, true)) return 1;
     if (copy_field(h, h->f[1], v_host, 0, true)) return 1;
     CK(cudaStreamSynchronize(h->s_compute));
+    return 0;
+}
+
+// Output without stalling the time loop (IO.write_step! every plotgap steps, IO.jl:82-96): a ghost-free
+// snapshot of u and v is taken on the update stream (device to device), then drained to the host on
+// a copy stream while later steps run.
+extern "C" int gsb_output_wait(gsb_t* h) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    if (h->copy_in_flight) {
+        CK(cudaEventSynchronize(h->ev_copied));
+        h->copy_in_flight = false;
+    }
+    return 0;
+}
+
+extern "C" int gsb_get_fields_async(gsb_t* h, void* u_host, void* v_host) {
+    if (!h || !u_host || !v_host) return fail("gsb_get_fields_async: null argument");
+    CK(cudaSetDevice(h->device));
+    const Layout& L = h->L;
+    const size_t nx = (size_t)L.sx, ny = (size_t)L.sy, nz = (size_t)L.sz;
+    const size_t bytes = nx * ny * nz * h->es;
+    for (int i = 0; i < 2; ++i)
+        if (!h->stage[i]) {
+            cudaError_t e = cudaMalloc(&h->stage[i], bytes);
+            if (e != cudaSuccess) {                 // no room for a snapshot (L = 2048 on one GPU): plain get
+                cudaGetLastError();
+                if (i == 1) { cudaFree(h->stage[0]); h->stage[0] = nullptr; }
+                h->stage[i] = nullptr;
+                return gsb_get_fields(h, u_host, v_host);
+            }
+        }
+    if (gsb_output_wait(h)) return 1;               // the staging buffers are free again
+    void* host[2] = {u_host, v_host};
+    for (int i = 0; i < 2; ++i) {
+        cudaMemcpy3DParms p;
+        memset(&p, 0, sizeof p);
+        p.srcPtr = make_cudaPitchedPtr(h->f[i], (size_t)L.px * h->es, (size_t)L.px * h->es, (size_t)(L.sy + 2));
+        p.srcPos = make_cudaPos((size_t)L.xoff * h->es, 1, 1);
+        p.dstPtr = make_cudaPitchedPtr(h->stage[i], nx * h->es, nx * h->es, ny);
+        p.dstPos = make_cudaPos(0, 0, 0);
+        p.extent = make_cudaExtent(nx * h->es, ny, nz);
+        p.kind = cudaMemcpyDeviceToDevice;
+        CK(cudaMemcpy3DAsync(&p, h->s_compute));
+    }
+    CK(cudaEventRecord(h->ev_snap, h->s_compute));
+    CK(cudaStreamWaitEvent(h->s_copy, h->ev_snap, 0));
+    for (int i = 0; i < 2; ++i) CK(cudaMemcpyAsync(host[i], h->stage[i], bytes, cudaMemcpyDeviceToHost, h->s_copy));
+    CK(cudaEventRecord(h->ev_copied, h->s_copy));
+    h->copy_in_flight = true;
     return 0;
 }
 
@@ -583,8 +660,9 @@ extern "C" int gsb_comm_init_local(gsb_t** hs, int n) {
 // ------------------------------------------------------------------ step orchestration
 static Box full_box(const gsb_handle* h) { return Box{0, h->L.sx, 0, h->L.sy, 0, h->L.sz}; }
 
-static int launch_box(gsb_handle* h, const Box& b, const Params& p) {
-    CK(launch_stencil(h->kcfg, h->f[0], h->f[1], h->f[2], h->f[3], &h->map[0], &h->map[1], h->L, p, b, h->s_compute));
+static int launch_box(gsb_handle* h, const Box& b, const Params& p, cudaStream_t st = nullptr) {
+    CK(launch_stencil(h->kcfg, h->f[0], h->f[1], h->f[2], h->f[3], &h->map[0], &h->map[1], h->L, p, b,
+                      st ? st : h->s_compute));
     h->launches += 1;
     return 0;
 }
@@ -648,11 +726,11 @@ static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, c
         fs.z0[fs.n] = pc.z0; fs.z1[fs.n] = pc.z1;
         fs.n++;
     }
-    if (fs.n) {
+    if (fs.n && !(debug_skip() & 1)) {
         CK(launch_pack_faces(h->cfg.dtype, h->f[2 * src], h->f[2 * src + 1], h->L, fs, h->s_comm));
         h->launches += 1;
     }
-    if (h->transport == TR_NCCL) {
+    if (h->transport == TR_NCCL && !(debug_skip() & 2)) {
         const ncclDataType_t ty = h->cfg.dtype == GSB_F32 ? ncclFloat : ncclDouble;
         NK(g_nccl.GroupStart());
         for (int d = 0; d < 6; ++d) {
@@ -682,7 +760,7 @@ static int enqueue_unpack(gsb_handle* h, const Piece& pc, int dst, int par, cuda
         fs.z0[fs.n] = pc.z0; fs.z1[fs.n] = pc.z1;
         fs.n++;
     }
-    if (fs.n) {
+    if (fs.n && !(debug_skip() & 4)) {
         CK(launch_unpack_faces(h->cfg.dtype, h->f[2 * dst], h->f[2 * dst + 1], h->L, fs, h->s_comm));
         h->launches += 1;
     }
@@ -742,9 +820,10 @@ static int enqueue_exchange_now(gsb_handle* h, bool local_second_half) {
 // chunk of the next step waits only for its own piece, which by then is most of a step old.
 static int pipeline_chunks(const gsb_handle* h) {
     if (!h->n_active) return 1;
-    int c = h->halo_chunks > 0 ? h->halo_chunks : (h->L.sz >= 256 ? 8 : h->L.sz / 32);
+    const int sz = h->L.sz;
+    int c = h->halo_chunks > 0 ? h->halo_chunks : (sz >= 512 ? 4 : sz >= 192 ? 3 : sz >= 32 ? 2 : 1);
     if (c > GSB_MAX_CHUNKS) c = GSB_MAX_CHUNKS;
-    if (c > h->L.sz) c = h->L.sz;
+    if (c > sz) c = sz;
     return c < 1 ? 1 : c;
 }
 
@@ -773,17 +852,24 @@ static Piece chunk_piece(const gsb_handle* h, int k, int C) {
 // which piece event chunk k must see before it may read its ghosts (events complete in visiting order)
 static int chunk_dependency(int k, int C) { return (k == 0 || k == C - 1) ? 0 : k; }
 
-static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, bool first, bool last) {
+static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, int i) {
     CK(cudaSetDevice(h->device));
+    const bool first = i == 0, last = i == C - 1;
+    cudaStream_t st = (i & 1) ? h->s_compute2 : h->s_compute;   // chunks are independent of one another
     if (first) {
         if (ensure_maps(h)) return 1;
         if (h->timers_on) CK(cudaEventRecord(h->tev[2], h->s_compute));
     }
-    if (h->n_active) CK(cudaStreamWaitEvent(h->s_compute, h->ev_piece[chunk_dependency(k, C)], 0));
+    if (i == 1) CK(cudaStreamWaitEvent(h->s_compute2, h->ev_compute, 0));   // previous step is complete
+    if (h->n_active) CK(cudaStreamWaitEvent(st, h->ev_piece[chunk_dependency(k, C)], 0));
     const Piece pc = chunk_piece(h, k, C);
-    if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p)) return 1;
-    CK(cudaEventRecord(h->ev_chunk, h->s_compute));
+    if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p, st)) return 1;
+    CK(cudaEventRecord(h->ev_chunk, st));
     if (last) {
+        if (C > 1) {                                             // join the second stream into the first
+            CK(cudaEventRecord(h->ev_join, h->s_compute2));
+            CK(cudaStreamWaitEvent(h->s_compute, h->ev_join, 0));
+        }
         if (h->timers_on) {
             CK(cudaEventRecord(h->tev[3], h->s_compute)); CK(cudaEventRecord(h->tev[5], h->s_compute));
             CK(cudaEventRecord(h->tev[4], h->s_compute));
@@ -820,7 +906,7 @@ static int pipeline_step(gsb_handle** hs, int n) {
         const int k = order[i];
         for (int r = 0; r < n; ++r) {
             gsb_handle* h = hs[r];
-            if (pipeline_compute_chunk(h, k, C, ps[r], i == 0, i == C - 1)) return 1;
+            if (pipeline_compute_chunk(h, k, C, ps[r], i)) return 1;
             if (h->n_active)
                 if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk)) return 1;
         }

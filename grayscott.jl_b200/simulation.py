@@ -334,6 +334,15 @@ def get_fields(fields: Fields, out=None):
     return u, v
 
 
+def get_fields_async(fields: Fields, u_host_ptr: int, v_host_ptr: int) -> None:
+    """Non-blocking get_fields into caller-owned (pinned) host memory; pair with output_wait."""
+    check(lib().gsb_get_fields_async(fields.handle, u_host_ptr, v_host_ptr))
+
+
+def output_wait(fields: Fields) -> None:
+    check(lib().gsb_output_wait(fields.handle))
+
+
 def calculate_arrays(u_dev_ptr, v_dev_ptr, u_out_ptr, v_out_ptr, sizes, T, settings: Settings, *,
                      offsets=(0, 0, 0), seed=DEFAULT_SEED, step=0, arith=_lib.GSB_ARITH_REFERENCE, stream=None):
     """One calculate! on device arrays in the reference layout (raw device pointers as ints)."""

@@ -142,6 +142,15 @@ int gsb_step_group(gsb_t** hs, int n, int nsteps);
  * (pinned memory makes it faster; pageable works).  Synchronises. */
 int gsb_get_fields(gsb_t* h, void* u_host, void* v_host);
 
+/* The same copies without stalling the time loop (IO.write_step! runs every `plotgap` steps,
+ * src/simulation/IO.jl:82-96, src/GrayScott.jl:86-95): a ghost-free snapshot is taken on the device
+ * in stream order, then drained to the (preferably pinned) host buffers on a copy stream while
+ * later steps run.  The host buffers are valid after gsb_output_wait (or the next
+ * gsb_get_fields_async, which waits for the previous one).  Needs 2 * sx*sy*sz * sizeof(T) bytes of
+ * extra device memory, allocated on first use; when that does not fit it degrades to gsb_get_fields. */
+int gsb_get_fields_async(gsb_t* h, void* u_host, void* v_host);
+int gsb_output_wait(gsb_t* h);
+
 /* Array(fields.<which>) / copyto!: the ghosted (sx+2)(sy+2)(sz+2) array in the reference
  * layout, from / to HOST memory.  For tests and restart.  Synchronise. */
 int gsb_get_ghosted(gsb_t* h, int which, void* host);

@@ -270,6 +270,24 @@ def test_exchange_calculate_swap_equals_iterate(sim):
     b.close()
 
 
+def test_async_output_equals_blocking_get_fields(sim):
+    """gsb_get_fields_async snapshots in stream order: steps enqueued after it must not leak into it."""
+    import torch
+    s, mcd, f = make(sim, 96, "Float32", noise=0.1)
+    sim.iterate(f, s, mcd, nsteps=5)
+    want_u, want_v = sim.get_fields(f)
+    hu = torch.empty(96 ** 3, dtype=torch.float32).pin_memory()
+    hv = torch.empty(96 ** 3, dtype=torch.float32).pin_memory()
+    for _ in range(2):                                   # second round reuses the staging buffers
+        sim.get_fields_async(f, hu.data_ptr(), hv.data_ptr())
+        sim.iterate(f, s, mcd, nsteps=7)                 # keeps running while the copy drains
+        sim.output_wait(f)
+        assert np.array_equal(hu.numpy().reshape(96, 96, 96), want_u)
+        assert np.array_equal(hv.numpy().reshape(96, 96, 96), want_v)
+        want_u, want_v = sim.get_fields(f)
+    f.close()
+
+
 def test_errors(sim):
     with pytest.raises(sim.GsbError, match="odd"):
         make(sim, 7, "Float32")                         # Int64(L/2 - 6): InexactError in the reference
