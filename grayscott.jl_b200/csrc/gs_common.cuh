@@ -80,5 +80,13 @@ template <typename T>
 __device__ __forceinline__ void st_vec(T* p, const Vec<T>& v) {
     *reinterpret_cast<Vec<T>*>(p) = v;
 }
+// streaming store (st.global.cs): the results are not read again before the next step, so they should
+// not displace the halo rows and planes that neighbouring CTAs are about to re-read from L2
+__device__ __forceinline__ void st_vec_stream(float* p, const Vec<float>& v) {
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v.a[0], v.a[1], v.a[2], v.a[3]));
+}
+__device__ __forceinline__ void st_vec_stream(double* p, const Vec<double>& v) {
+    __stcs(reinterpret_cast<double2*>(p), make_double2(v.a[0], v.a[1]));
+}
 
 }  // namespace gsb

@@ -59,8 +59,8 @@ __device__ __forceinline__ void store_masked(T* pu, T* pv, const Vec<T>& uo, con
                                              int bx1) {
     constexpr int N = Vec<T>::N;
     if (x >= bx0 && x + N <= bx1) {
-        st_vec(pu, uo);
-        st_vec(pv, vo);
+        st_vec_stream(pu, uo);
+        st_vec_stream(pv, vo);
     } else {
 #pragma unroll
         for (int i = 0; i < N; ++i)
