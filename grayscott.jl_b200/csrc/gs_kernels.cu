@@ -2,6 +2,7 @@
 // the TMA tensor-map encoder and the dtype dispatch of the stencil launchers.
 #include <cfloat>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "gs_kernels.h"
@@ -54,9 +55,16 @@ int make_field_tensor_map(CUtensorMap* out, int dtype, const void* base, const L
     cuuint64_t strides[2] = {(cuuint64_t)L.px * es, (cuuint64_t)L.pxy * es};
     cuuint32_t box[3] = {(cuuint32_t)(32 * n + 2 * n), (cuuint32_t)(ty + 2), 1};
     cuuint32_t estr[3] = {1, 1, 1};
+    // L2 promotion (fetch granularity of the TMA reads): $GSB_TMA_L2PROMO = 0 | 64 | 128 | 256
+    CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    if (const char* e = getenv("GSB_TMA_L2PROMO")) {
+        const int v = atoi(e);
+        promo = v == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : v == 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+              : v == 256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    }
     CUresult r = fn(out, dtype == DT_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3,
                     const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    CU_TENSOR_MAP_SWIZZLE_NONE, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         static thread_local char msg[96];
         snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
