@@ -371,6 +371,33 @@ def test_halo_exchange_bit_exact_vs_single_subdomain(sim, orc, monkeypatch, prec
     one.close()
 
 
+@pytest.mark.parametrize("nranks,L", [(3, 48), (6, 48), (12, 48), (27, 54)])
+@pytest.mark.parametrize("scheme", [("pipeline", None), ("pipeline", 3), ("split", None)])
+def test_halo_exchange_other_decompositions(sim, orc, monkeypatch, nranks, L, scheme):
+    """Decompositions with interior ranks (two neighbours per dimension) and unequal dims:
+    3 -> (3,1,1), 6 -> (3,2,1), 12 -> (3,2,2), 27 -> (3,3,3); against the oracle's N-rank run."""
+    monkeypatch.setenv("GSB_HALO", scheme[0])
+    if scheme[1]:
+        monkeypatch.setenv("GSB_HALO_CHUNKS", str(scheme[1]))
+    else:
+        monkeypatch.delenv("GSB_HALO_CHUNKS", raising=False)
+    steps, prec = 9, "Float32"
+    s = settings(sim, L, prec, 0.1)
+    ranks = []
+    for r in range(nranks):
+        mcd = sim.init_domain(s, r, nranks)
+        ranks.append((mcd, sim.init_fields(s, mcd, prec, seed=4)))
+    sim.connect_local([f for _, f in ranks])
+    sim.iterate_group([f for _, f in ranks], s, nsteps=steps)
+    o = orc.Oracle(L, prec, dims=orc.dims_create(nranks), noise=0.1, seed=4, **PHYS)
+    o.step(steps)
+    for r, (mcd, f) in enumerate(ranks):
+        u, v = sim.get_fields(f)
+        uo, vo = o.get_fields(r)
+        assert np.array_equal(u, uo) and np.array_equal(v, vo), r
+        f.close()
+
+
 @pytest.mark.parametrize("scheme", ["pipeline", "split"])
 def test_overlap_large_subdomains(sim, monkeypatch, scheme):
     """Subdomains big enough that the interior/shell split is active in every direction and that the

@@ -26,6 +26,23 @@ def test_library_exports_every_declared_symbol(pkg):
     assert pkg._lib.lib().gsb_version() == 100
 
 
+def test_header_is_valid_c_and_links(pkg, tmp_path):
+    """A C program that includes include/gsb200.h, takes the address of every entry point and calls the
+    GPU-free ones: what a C / ccall / cgo-style binding would see."""
+    exe = tmp_path / "header_check"
+    libdir = os.path.dirname(pkg.LIB_PATH)
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
+    r = subprocess.run([cc, "-std=c11", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "tests", "header_check.c"), "-o", str(exe), "-L", libdir, "-lgsb200",
+                        f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "35 symbols, version 100" in r.stdout
+    # the Python mirror of struct gsb_config has the same size as the C one
+    assert f"sizeof(gsb_config) = {C.sizeof(pkg._lib.GsbConfig)}" in r.stdout
+
+
 def test_product_never_touches_the_oracle():
     """The oracle is test infrastructure: nothing under grayscott.jl_b200/ may name it."""
     for dirpath, _, files in os.walk(os.path.join(ROOT, "grayscott.jl_b200")):
