@@ -36,6 +36,20 @@ static int fail(const char* fmt, ...) {
             return fail("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));        \
     } while (0)
 
+// Makes `dev` current for the duration of a call and restores the caller's device afterwards (the host
+// process -- Julia with CUDA.jl, Python with torch -- has its own notion of the current device).
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int dev) {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
 // ------------------------------------------------------------------ NCCL, loaded lazily
 // dlopen instead of a link-time dependency: a process that already holds an NCCL (PyTorch's
 // bundled one) must keep exactly that copy.
@@ -277,7 +291,7 @@ extern "C" int gsb_fill_domain(gsb_config* c, int64_t L, int nranks, int rank) {
 
 extern "C" int gsb_destroy(gsb_t* h) {
     if (!h) return 0;
-    cudaSetDevice(h->device);
+    DeviceGuard guard_(h->device);
     cudaDeviceSynchronize();
     if (h->comm && g_nccl.lib) g_nccl.CommDestroy(h->comm);
     for (int i = 0; i < 4; ++i) if (h->f[i]) cudaFree(h->f[i]);
@@ -324,7 +338,8 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
     }
     h->es = c.dtype == GSB_F32 ? 4 : 8;
     h->device = c.device;
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, h->device));
     if (prop.major < 10) return fail("device %d is sm_%d%d; this library holds sm_100a code only", h->device, prop.major, prop.minor);
@@ -391,7 +406,8 @@ extern "C" int gsb_create(gsb_t** out, const gsb_config* cfg) {
 // ------------------------------------------------------------------ init / access
 extern "C" int gsb_init_fields(gsb_t* h) {
     if (!h) return fail("null handle");
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     const long long off[3] = {h->cfg.offsets[0], h->cfg.offsets[1], h->cfg.offsets[2]};
     CK(cudaStreamSynchronize(h->s_comm));      // no halo piece may still be landing in the ghosts
     CK(cudaStreamSynchronize(h->s_compute));
@@ -404,7 +420,8 @@ extern "C" int gsb_init_fields(gsb_t* h) {
 
 extern "C" int gsb_sync(gsb_t* h) {
     if (!h) return fail("null handle");
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamSynchronize(h->s_comm));
     CK(cudaStreamSynchronize(h->s_compute));
     return 0;
@@ -430,7 +447,8 @@ static int copy_field(gsb_handle* h, void* dev, void* host, int g, bool to_host)
 
 extern "C" int gsb_get_fields(gsb_t* h, void* u_host, void* v_host) {
     if (!h || !u_host || !v_host) return fail("gsb_get_fields: null argument");
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamSynchronize(h->s_comm));
     if (copy_field(h, h->f[0], u_host, 0, true)) return 1;
     if (copy_field(h, h->f[1], v_host, 0, true)) return 1;
@@ -443,7 +461,8 @@ extern "C" int gsb_get_fields(gsb_t* h, void* u_host, void* v_host) {
 // a copy stream while later steps run.
 extern "C" int gsb_output_wait(gsb_t* h) {
     if (!h) return fail("null handle");
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     if (h->copy_in_flight) {
         CK(cudaEventSynchronize(h->ev_copied));
         h->copy_in_flight = false;
@@ -453,7 +472,8 @@ extern "C" int gsb_output_wait(gsb_t* h) {
 
 extern "C" int gsb_get_fields_async(gsb_t* h, void* u_host, void* v_host) {
     if (!h || !u_host || !v_host) return fail("gsb_get_fields_async: null argument");
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     const Layout& L = h->L;
     const size_t nx = (size_t)L.sx, ny = (size_t)L.sy, nz = (size_t)L.sz;
     const size_t bytes = nx * ny * nz * h->es;
@@ -491,7 +511,8 @@ extern "C" int gsb_get_fields_async(gsb_t* h, void* u_host, void* v_host) {
 extern "C" int gsb_get_ghosted(gsb_t* h, int which, void* host) {
     if (!h || !host) return fail("gsb_get_ghosted: null argument");
     if (which < 0 || which > 3) return fail("gsb_get_ghosted: which = %d", which);
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamSynchronize(h->s_comm));
     if (copy_field(h, h->f[which], host, 1, true)) return 1;
     CK(cudaStreamSynchronize(h->s_compute));
@@ -501,7 +522,8 @@ extern "C" int gsb_get_ghosted(gsb_t* h, int which, void* host) {
 extern "C" int gsb_set_ghosted(gsb_t* h, int which, const void* host) {
     if (!h || !host) return fail("gsb_set_ghosted: null argument");
     if (which < 0 || which > 3) return fail("gsb_set_ghosted: which = %d", which);
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamSynchronize(h->s_comm));
     if (copy_field(h, h->f[which], const_cast<void*>(host), 1, false)) return 1;
     h->ghost_valid = false;
@@ -534,7 +556,8 @@ extern "C" int gsb_set_step(gsb_t* h, int64_t step) {
 extern "C" int gsb_field_stats(gsb_t* h, int which, double thresh, double out[5]) {
     if (!h || !out) return fail("null argument");
     if (which < 0 || which > 3) return fail("gsb_field_stats: which = %d", which);
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamSynchronize(h->s_comm));
     CK(launch_field_stats(h->cfg.dtype, h->f[which], h->L, thresh, h->stats_partials, h->stats_out, h->s_compute));
     CK(cudaMemcpyAsync(out, h->stats_out, sizeof(double) * 5, cudaMemcpyDeviceToHost, h->s_compute));
@@ -552,7 +575,8 @@ extern "C" int gsb_set_kernel(gsb_t* h, int kind, int ty, int stages, int zchunk
     if (stages > 0) k.stages = stages;
     if (zchunk > 0) k.zchunk = zchunk;
     if (!kernel_shape_ok(k)) return fail("kernel shape kind=%d ty=%d stages=%d is not instantiated", k.kind, k.ty, k.stages);
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     h->kcfg = k;
     return ensure_maps(h);
 }
@@ -615,7 +639,8 @@ extern "C" int gsb_comm_init(gsb_t* h, const void* id128) {
     if (!h || !id128) return fail("null argument");
     if (h->transport != TR_NONE) return fail("communication already initialised");
     if (nccl_load()) return 1;
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     ncclUniqueId id;
     memcpy(&id, id128, sizeof id);
     NK(g_nccl.CommInitRank(&h->comm, h->cfg.nranks, id, h->cfg.rank));
@@ -646,7 +671,8 @@ extern "C" int gsb_comm_init_local(gsb_t** hs, int n) {
                 int can = 0;
                 CK(cudaDeviceCanAccessPeer(&can, h->device, p->device));
                 if (!can) return fail("device %d cannot access device %d", h->device, p->device);
-                CK(cudaSetDevice(h->device));
+                DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
                 cudaError_t e = cudaDeviceEnablePeerAccess(p->device, 0);
                 if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
                 else CK(e);
@@ -713,7 +739,8 @@ static size_t piece_offset(const gsb_handle* h, int d, int z0) {
 //   src = 0: the fields as bound now (u, v); src = 1: the fields being written (u_temp, v_temp)
 //   par: which of the two receive buffers this exchange uses
 static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, cudaEvent_t after) {
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamWaitEvent(h->s_comm, after, 0));               // the cells to send are final
     if (h->timers_on) CK(cudaEventRecord(h->tev[0], h->s_comm));
     FaceSet fs;
@@ -747,7 +774,8 @@ static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, c
 
 // (wait for the neighbours) -> unpack into the ghosts of the fields `dst` (0: u, v; 1: u_temp, v_temp)
 static int enqueue_unpack(gsb_handle* h, const Piece& pc, int dst, int par, cudaEvent_t done) {
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     if (h->transport == TR_LOCAL)
         for (int d = 0; d < 6; ++d)
             if (pc.recv[d]) CK(cudaStreamWaitEvent(h->s_comm, h->peer[d]->ev_packed, 0));
@@ -777,7 +805,8 @@ static int check_transport(gsb_handle* h) {
 
 // ---- scheme A ("split"): exchange at the start of the step, interior update meanwhile, shell after
 static int enqueue_compute_overlapped(gsb_handle* h) {
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     if (ensure_maps(h)) return 1;
     const Params p = make_params(h);
     if (h->timers_on) CK(cudaEventRecord(h->tev[2], h->s_compute));
@@ -853,7 +882,8 @@ static Piece chunk_piece(const gsb_handle* h, int k, int C) {
 static int chunk_dependency(int k, int C) { return (k == 0 || k == C - 1) ? 0 : k; }
 
 static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, int i) {
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     const bool first = i == 0, last = i == C - 1;
     cudaStream_t st = (i & 1) ? h->s_compute2 : h->s_compute;   // chunks are independent of one another
     if (first) {
@@ -941,7 +971,8 @@ extern "C" int gsb_exchange(gsb_t* h) {
 
 extern "C" int gsb_calculate(gsb_t* h) {
     if (!h) return fail("null handle");
-    CK(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     if (ensure_maps(h)) return 1;
     const Params p = make_params(h);
     if (h->n_active) CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
