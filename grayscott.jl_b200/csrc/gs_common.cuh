@@ -63,6 +63,19 @@ struct Box {
     int x0, x1, y0, y1, z0, z1;
 };
 
+// X faces carried by the update kernel itself (pipelined halo scheme, sx a multiple of the tile
+// width): instead of a separate strided gather/scatter over 2 * sy * sz cells, the lane that owns
+// column x = 0 (x = sx-1) stores its new values into the dense message buffer and reads its W (E)
+// ghost from the dense receive buffer.  Layout of a piece [zbase, zbase+nz): [u | v], element
+// y + sy * (z - zbase); the v part starts sy * nz elements later.  Null pointers switch a role off.
+struct XFaceArgs {
+    const void* ghost_lo;   // W ghosts for column x = 0        (null: read the ghost column of the array)
+    const void* ghost_hi;   // E ghosts for column x = sx-1
+    void* send_lo;          // new values of column x = 0       (null: not sent by the kernel)
+    void* send_hi;          // new values of column x = sx-1
+    int zbase, nz;
+};
+
 enum : int { ARITH_REFERENCE = 0, ARITH_NATIVE = 1 };
 
 // 16-byte vector of T: float x4 or double x2.

@@ -11,16 +11,20 @@ namespace gsb {
 
 template <typename T>
 cudaError_t launch_stencil_T(const StencilCfg&, const void*, const void*, void*, void*, const CUtensorMap*,
-                             const CUtensorMap*, const Layout&, const Params&, const Box&, cudaStream_t);
+                             const CUtensorMap*, const Layout&, const Params&, const Box&, const XFaceArgs&, cudaStream_t);
 template <typename T>
 cudaError_t launch_naive_T(int, int, const void*, const void*, void*, void*, int, int, int, const Params&,
                            cudaStream_t);
 
 cudaError_t launch_stencil(const StencilCfg& c, const void* u, const void* v, void* uo, void* vo,
                            const CUtensorMap* mu, const CUtensorMap* mv, const Layout& L, const Params& p,
-                           const Box& box, cudaStream_t st) {
-    return c.dtype == DT_F32 ? launch_stencil_T<float>(c, u, v, uo, vo, mu, mv, L, p, box, st)
-                             : launch_stencil_T<double>(c, u, v, uo, vo, mu, mv, L, p, box, st);
+                           const Box& box, cudaStream_t st, const XFaceArgs* xface) {
+    XFaceArgs xf;
+    memset(&xf, 0, sizeof xf);
+    xf.nz = 1;
+    if (xface) xf = *xface;
+    return c.dtype == DT_F32 ? launch_stencil_T<float>(c, u, v, uo, vo, mu, mv, L, p, box, xf, st)
+                             : launch_stencil_T<double>(c, u, v, uo, vo, mu, mv, L, p, box, xf, st);
 }
 
 cudaError_t launch_naive_reflayout(int dtype, int arith, int noise, const void* u, const void* v, void* uo,

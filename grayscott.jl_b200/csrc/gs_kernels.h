@@ -25,7 +25,7 @@ struct StencilCfg {
 // gs_kernels.cu; launch_stencil returns cudaErrorInvalidConfiguration otherwise.
 cudaError_t launch_stencil(const StencilCfg& c, const void* u, const void* v, void* uo, void* vo,
                            const CUtensorMap* map_u, const CUtensorMap* map_v, const Layout& L, const Params& p,
-                           const Box& box, cudaStream_t st);
+                           const Box& box, cudaStream_t st, const XFaceArgs* xface = nullptr);
 
 // Tensor map over one padded field for the TMA kernel with `ty` rows per CTA.  Returns 0 on success.
 int make_field_tensor_map(CUtensorMap* out, int dtype, const void* base, const Layout& L, int ty, const char** err);

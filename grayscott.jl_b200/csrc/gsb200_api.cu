@@ -119,7 +119,7 @@ struct gsb_handle {
     bool copy_in_flight;
     cudaEvent_t ev_compute, ev_halo, ev_packed, ev_chunk;
     cudaEvent_t ev_piece[GSB_MAX_CHUNKS];   // pipelined halo: piece k of the previous step has landed
-    int halo_mode, halo_chunks;
+    int halo_mode, halo_chunks, fuse_x;
     bool ghost_valid;       // the ghosts of the current fields already hold the neighbours' current values
     long long step;
     StencilCfg kcfg;
@@ -367,6 +367,8 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
         h->halo_mode = (hm && !strcmp(hm, "split")) ? HALO_SPLIT : HALO_PIPELINE;
         const char* hc = getenv("GSB_HALO_CHUNKS");
         h->halo_chunks = hc ? atoi(hc) : 0;
+        const char* fx = getenv("GSB_FUSE_X");
+        h->fuse_x = fx ? atoi(fx) : 0;
     }
     for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&h->tev[i]));
     h->n_active = 0;
@@ -445,6 +447,8 @@ static int copy_field(gsb_handle* h, void* dev, void* host, int g, bool to_host)
     return 0;
 }
 
+static int refresh_x_ghosts(gsb_handle* h);
+
 extern "C" int gsb_get_fields(gsb_t* h, void* u_host, void* v_host) {
     if (!h || !u_host || !v_host) return fail("gsb_get_fields: null argument");
     DeviceGuard guard_(h->device);
@@ -514,6 +518,7 @@ extern "C" int gsb_get_ghosted(gsb_t* h, int which, void* host) {
     DeviceGuard guard_(h->device);
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamSynchronize(h->s_comm));
+    if (refresh_x_ghosts(h)) return 1;
     if (copy_field(h, h->f[which], host, 1, true)) return 1;
     CK(cudaStreamSynchronize(h->s_compute));
     return 0;
@@ -578,6 +583,7 @@ extern "C" int gsb_set_kernel(gsb_t* h, int kind, int ty, int stages, int zchunk
     DeviceGuard guard_(h->device);
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     h->kcfg = k;
+    h->ghost_valid = false;   // the kernel kind decides who carries the x faces
     return ensure_maps(h);
 }
 extern "C" int gsb_get_kernel(gsb_t* h, int* kind, int* ty, int* stages, int* zchunk) {
@@ -686,9 +692,10 @@ extern "C" int gsb_comm_init_local(gsb_t** hs, int n) {
 // ------------------------------------------------------------------ step orchestration
 static Box full_box(const gsb_handle* h) { return Box{0, h->L.sx, 0, h->L.sy, 0, h->L.sz}; }
 
-static int launch_box(gsb_handle* h, const Box& b, const Params& p, cudaStream_t st = nullptr) {
+static int launch_box(gsb_handle* h, const Box& b, const Params& p, cudaStream_t st = nullptr,
+                      const XFaceArgs* xf = nullptr) {
     CK(launch_stencil(h->kcfg, h->f[0], h->f[1], h->f[2], h->f[3], &h->map[0], &h->map[1], h->L, p, b,
-                      st ? st : h->s_compute));
+                      st ? st : h->s_compute, xf));
     h->launches += 1;
     return 0;
 }
@@ -715,6 +722,17 @@ static bool interior_box(const gsb_handle* h, Box* b) {
     return true;
 }
 
+// Optional ($GSB_FUSE_X=1 at gsb_create): the x faces ride inside the update kernel (XFaceArgs) when the
+// pipelined scheme runs the TMA kernel on a subdomain whose sx is a whole number of tiles.  It removes
+// the strided pack/unpack of 2 * sy * sz cells (~0.1 ms per step at 1024^3), but the XF instantiation
+// of the kernel currently executes ~40 % more instructions and loses more than that (measured
+// 3.7 vs 3.1 ms per step), so it is OFF by default; kept because it is bit-exact and tested.
+static bool fused_x(const gsb_handle* h) {
+    const int tile = 32 * (int)(16 / h->es);
+    return h->fuse_x && h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
+           (h->active[GSB_WEST] || h->active[GSB_EAST]) && h->L.sx % tile == 0;
+}
+
 // A piece of the halo: which faces travel, and for the x / y faces which z range.
 struct Piece {
     int z0, z1;
@@ -738,7 +756,7 @@ static size_t piece_offset(const gsb_handle* h, int d, int z0) {
 // pack -> (transport): first half of an exchange, on the communication stream.
 //   src = 0: the fields as bound now (u, v); src = 1: the fields being written (u_temp, v_temp)
 //   par: which of the two receive buffers this exchange uses
-static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, cudaEvent_t after) {
+static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, cudaEvent_t after, bool xfused = false) {
     DeviceGuard guard_(h->device);
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamWaitEvent(h->s_comm, after, 0));               // the cells to send are final
@@ -747,6 +765,7 @@ static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, c
     fs.n = 0;
     for (int d = 0; d < 6; ++d) {
         if (!pc.send[d]) continue;
+        if (d < 2 && src == 1 && xfused) continue;              // the update kernel wrote this message itself
         char* base = (char*)(h->transport == TR_LOCAL ? h->peer[d]->recv[par][opp(d)] : h->send[d]);
         fs.dir[fs.n] = d;
         fs.buf[fs.n] = base + piece_offset(h, d, pc.z0);
@@ -773,7 +792,7 @@ static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, c
 }
 
 // (wait for the neighbours) -> unpack into the ghosts of the fields `dst` (0: u, v; 1: u_temp, v_temp)
-static int enqueue_unpack(gsb_handle* h, const Piece& pc, int dst, int par, cudaEvent_t done) {
+static int enqueue_unpack(gsb_handle* h, const Piece& pc, int dst, int par, cudaEvent_t done, bool xfused = false) {
     DeviceGuard guard_(h->device);
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     if (h->transport == TR_LOCAL)
@@ -783,6 +802,7 @@ static int enqueue_unpack(gsb_handle* h, const Piece& pc, int dst, int par, cuda
     fs.n = 0;
     for (int d = 0; d < 6; ++d) {
         if (!pc.recv[d]) continue;
+        if (d < 2 && xfused) continue;                          // the update kernel reads the receive buffer
         fs.dir[fs.n] = d;
         fs.buf[fs.n] = (char*)h->recv[par][d] + piece_offset(h, d, pc.z0);
         fs.z0[fs.n] = pc.z0; fs.z1[fs.n] = pc.z1;
@@ -878,6 +898,27 @@ static Piece chunk_piece(const gsb_handle* h, int k, int C) {
     return p;
 }
 
+// x-face arguments of chunk k for the update kernel (fused scheme); `step_par` = parity of the step
+// whose ghosts are READ, the new values go to the other parity
+static XFaceArgs chunk_xface(const gsb_handle* h, int k, int C) {
+    XFaceArgs xf;
+    memset(&xf, 0, sizeof xf);
+    const Piece pc = chunk_piece(h, k, C);
+    xf.zbase = pc.z0;
+    xf.nz = pc.z1 - pc.z0;
+    const int rd = (int)(h->step & 1), wr = (int)((h->step + 1) & 1);
+    auto at = [&](void* base, int d) { return (void*)((char*)base + piece_offset(h, d, pc.z0)); };
+    if (h->active[GSB_WEST]) {
+        xf.ghost_lo = at(h->recv[rd][GSB_WEST], GSB_WEST);
+        xf.send_lo = at(h->transport == TR_LOCAL ? h->peer[GSB_WEST]->recv[wr][GSB_EAST] : h->send[GSB_WEST], GSB_WEST);
+    }
+    if (h->active[GSB_EAST]) {
+        xf.ghost_hi = at(h->recv[rd][GSB_EAST], GSB_EAST);
+        xf.send_hi = at(h->transport == TR_LOCAL ? h->peer[GSB_EAST]->recv[wr][GSB_WEST] : h->send[GSB_EAST], GSB_EAST);
+    }
+    return xf;
+}
+
 // which piece event chunk k must see before it may read its ghosts (events complete in visiting order)
 static int chunk_dependency(int k, int C) { return (k == 0 || k == C - 1) ? 0 : k; }
 
@@ -893,7 +934,10 @@ static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, 
     if (i == 1) CK(cudaStreamWaitEvent(h->s_compute2, h->ev_compute, 0));   // previous step is complete
     if (h->n_active) CK(cudaStreamWaitEvent(st, h->ev_piece[chunk_dependency(k, C)], 0));
     const Piece pc = chunk_piece(h, k, C);
-    if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p, st)) return 1;
+    if (fused_x(h)) {
+        const XFaceArgs xf = chunk_xface(h, k, C);
+        if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p, st, &xf)) return 1;
+    } else if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p, st)) return 1;
     CK(cudaEventRecord(h->ev_chunk, st));
     if (last) {
         if (C > 1) {                                             // join the second stream into the first
@@ -910,16 +954,56 @@ static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, 
     return 0;
 }
 
-// bring the ghosts of the current fields up to date once (first step after init / set / piecewise use)
+// bring the ghosts of the current fields up to date once (first step after init / set / piecewise use):
+// the same pieces, in the same order and message layout as the steady state, but packed from the
+// CURRENT fields
 static int pipeline_prime(gsb_handle** hs, int n) {
     bool need = false;
     for (int r = 0; r < n; ++r) need = need || (hs[r]->n_active && !hs[r]->ghost_valid);
     if (!need) return 0;
-    for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_exchange_now(hs[r], false)) return 1;
+    const int C = pipeline_chunks(hs[0]);
+    int order[GSB_MAX_CHUNKS];
+    chunk_order(C, order);
+    for (int i = 0; i < C; ++i) {
+        const int k = order[i];
+        for (int r = 0; r < n; ++r) {
+            gsb_handle* h = hs[r];
+            if (h->n_active) if (enqueue_pack_send(h, chunk_piece(h, k, C), 0, (int)(h->step & 1), h->ev_compute)) return 1;
+        }
+        for (int r = 0; r < n; ++r) {
+            gsb_handle* h = hs[r];
+            if (h->n_active)
+                if (enqueue_unpack(h, chunk_piece(h, k, C), 0, (int)(h->step & 1), h->ev_piece[k], fused_x(h))) return 1;
+        }
+    }
     for (int r = 0; r < n; ++r) if (hs[r]->n_active) {
-        if (enqueue_exchange_now(hs[r], true)) return 1;
-        for (int k = 0; k < GSB_MAX_CHUNKS; ++k) CK(cudaEventRecord(hs[r]->ev_piece[k], hs[r]->s_comm));
+        // unused piece events (k >= C) must not hold stale records of an earlier chunk count
+        DeviceGuard guard_(hs[r]->device);
+        for (int k = C; k < GSB_MAX_CHUNKS; ++k) CK(cudaEventRecord(hs[r]->ev_piece[k], hs[r]->s_comm));
         hs[r]->ghost_valid = true;
+    }
+    return 0;
+}
+
+// Array(fields.u) must show the neighbours' columns although, in the fused scheme, the kernels read
+// them from the receive buffers: copy them into the ghost columns of the current fields on demand.
+static int refresh_x_ghosts(gsb_handle* h) {
+    if (!h->n_active || !h->ghost_valid || !fused_x(h)) return 0;
+    const int C = pipeline_chunks(h);
+    for (int k = 0; k < C; ++k) {
+        Piece pc = chunk_piece(h, k, C);
+        for (int d = 2; d < 6; ++d) pc.recv[d] = false;
+        // unpack only (no neighbour wait: the data landed before ghost_valid was set; callers synchronised s_comm)
+        FaceSet fs;
+        fs.n = 0;
+        for (int d = 0; d < 2; ++d) {
+            if (!pc.recv[d]) continue;
+            fs.dir[fs.n] = d;
+            fs.buf[fs.n] = (char*)h->recv[h->step & 1][d] + piece_offset(h, d, pc.z0);
+            fs.z0[fs.n] = pc.z0; fs.z1[fs.n] = pc.z1;
+            fs.n++;
+        }
+        if (fs.n) CK(launch_unpack_faces(h->cfg.dtype, h->f[0], h->f[1], h->L, fs, h->s_compute));
     }
     return 0;
 }
@@ -938,12 +1022,12 @@ static int pipeline_step(gsb_handle** hs, int n) {
             gsb_handle* h = hs[r];
             if (pipeline_compute_chunk(h, k, C, ps[r], i)) return 1;
             if (h->n_active)
-                if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk)) return 1;
+                if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk, fused_x(h))) return 1;
         }
         for (int r = 0; r < n; ++r) {
             gsb_handle* h = hs[r];
             if (h->n_active)
-                if (enqueue_unpack(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_piece[k])) return 1;
+                if (enqueue_unpack(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_piece[k], fused_x(h))) return 1;
         }
     }
     for (int r = 0; r < n; ++r) { swap_bindings(hs[r]); hs[r]->ghost_valid = hs[r]->n_active > 0; }
@@ -965,7 +1049,7 @@ extern "C" int gsb_exchange(gsb_t* h) {
     if (h->transport == TR_LOCAL) return fail("gsb_exchange: in-process handles advance together, use gsb_step_group");
     if (enqueue_exchange_now(h, false)) return 1;
     if (enqueue_exchange_now(h, true)) return 1;
-    h->ghost_valid = true;
+    h->ghost_valid = false;   // whole-face message layout: a later gsb_step exchanges again in its own layout
     return 0;
 }
 

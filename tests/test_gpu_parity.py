@@ -398,6 +398,47 @@ def test_halo_exchange_other_decompositions(sim, orc, monkeypatch, nranks, L, sc
         f.close()
 
 
+@pytest.mark.parametrize("prec", ["Float32", "Float64"])
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+@pytest.mark.parametrize("chunks", [None, 1, 3])
+def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nranks, chunks):
+    """Optional scheme (GSB_FUSE_X=1): sx = 128 is a whole number of tiles, so the update kernel can
+    write its boundary columns into the message buffers and read its x ghosts from the receive buffers
+    (no strided pack/unpack).  Must equal the oracle's N-rank run bit for bit, and Array(fields.u) must
+    still show the neighbour's column in the ghost layer."""
+    monkeypatch.setenv("GSB_HALO", "pipeline")
+    monkeypatch.setenv("GSB_FUSE_X", "1")
+    if chunks:
+        monkeypatch.setenv("GSB_HALO_CHUNKS", str(chunks))
+    else:
+        monkeypatch.delenv("GSB_HALO_CHUNKS", raising=False)
+    L, steps = 256, 7
+    s = settings(sim, L, prec, 0.1)
+    ranks = []
+    for r in range(nranks):
+        mcd = sim.init_domain(s, r, nranks)
+        ranks.append((mcd, sim.init_fields(s, mcd, prec, seed=13)))
+    assert ranks[0][0].proc_sizes[0] == 128
+    sim.connect_local([f for _, f in ranks])
+    sim.iterate_group([f for _, f in ranks], s, nsteps=3)
+    sim.iterate_group([f for _, f in ranks], s, nsteps=steps - 3)
+    o = orc.Oracle(L, prec, dims=orc.dims_create(nranks), noise=0.1, seed=13, **PHYS)
+    o.step(steps)
+    got = []
+    for r, (mcd, f) in enumerate(ranks):
+        u, v = sim.get_fields(f)
+        uo, vo = o.get_fields(r)
+        assert np.array_equal(u, uo) and np.array_equal(v, vo), r
+        got.append(u)
+    # rank 0's east ghost column is its east neighbour's column x = 0 (current values)
+    mcd0, f0 = ranks[0]
+    east = mcd0.proc_neighbors["east"]
+    g = np.asarray(f0.u)
+    assert np.array_equal(g[1:-1, 1:-1, -1], got[east][:, :, 0])
+    for _, f in ranks:
+        f.close()
+
+
 @pytest.mark.parametrize("scheme", ["pipeline", "split"])
 def test_overlap_large_subdomains(sim, monkeypatch, scheme):
     """Subdomains big enough that the interior/shell split is active in every direction and that the
