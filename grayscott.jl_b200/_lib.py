@@ -62,6 +62,7 @@ _PROTOS = [
     ("gsb_get_step", _i, [_vp, C.POINTER(_i64)]),
     ("gsb_set_step", _i, [_vp, _i64]),
     ("gsb_field_stats", _i, [_vp, _i, C.c_double, C.POINTER(C.c_double)]),
+    ("gsb_pdf", _i, [_vp, _i, _i, C.c_double, C.c_double, _vp, _vp]),
     ("gsb_get_unique_id", _i, [_vp]),
     ("gsb_comm_init", _i, [_vp, _vp]),
     ("gsb_comm_init_local", _i, [C.POINTER(_vp), _i]),

@@ -208,6 +208,43 @@ cudaError_t launch_unpack_faces(int dtype, void* u, void* v, const Layout& L, co
     return faces_launch<false>(dtype, u, v, L, fs, st);
 }
 
+// ------------------------------------------------------------------ per-slice PDF
+// _compute_pdf (src/analysis/pdfcalc.jl:13-49, unfinished in the reference): for every z slice a
+// histogram of `nbins` equal bins over [min, max]; bin = floor((value - min) / bin_width) evaluated in
+// T, value == max falls into the last bin, values outside the range are not counted.
+template <typename T>
+__global__ void pdf_kernel(const T* __restrict__ f, Layout L, int nbins, T vmin, T vmax, T bin_width,
+                           unsigned* __restrict__ pdf) {
+    extern __shared__ unsigned hist[];
+    for (int b = threadIdx.x; b < nbins; b += blockDim.x) hist[b] = 0;
+    __syncthreads();
+    const int z = blockIdx.x;
+    const long long cells = (long long)L.sx * L.sy;
+    for (long long c = threadIdx.x; c < cells; c += blockDim.x) {
+        const int y = (int)(c / L.sx), x = (int)(c % L.sx);
+        const T v = f[L.idx(x, y, z)];
+        if (v < vmin || v > vmax) continue;
+        int bin = (int)floor((v - vmin) / bin_width);
+        if (bin >= nbins) bin = nbins - 1;
+        atomicAdd(&hist[bin], 1u);
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < nbins; b += blockDim.x) pdf[(long long)z * nbins + b] = hist[b];
+}
+
+cudaError_t launch_pdf(int dtype, const void* f, const Layout& L, int nbins, double vmin, double vmax,
+                       unsigned* pdf_dev, cudaStream_t st) {
+    const size_t smem = sizeof(unsigned) * (size_t)nbins;
+    if (dtype == DT_F32) {
+        const float lo = (float)vmin, hi = (float)vmax, w = (hi - lo) / (float)nbins;
+        pdf_kernel<float><<<L.sz, 256, smem, st>>>((const float*)f, L, nbins, lo, hi, w, pdf_dev);
+    } else {
+        const double w = (vmax - vmin) / (double)nbins;
+        pdf_kernel<double><<<L.sz, 256, smem, st>>>((const double*)f, L, nbins, vmin, vmax, w, pdf_dev);
+    }
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ statistics
 static constexpr int STATS_BLOCKS = 148 * 4;
 static constexpr int STATS_THREADS = 256;

@@ -57,6 +57,10 @@ cudaError_t launch_pack_faces(int dtype, const void* u, const void* v, const Lay
                               cudaStream_t st);
 cudaError_t launch_unpack_faces(int dtype, void* u, void* v, const Layout& L, const FaceSet& fs, cudaStream_t st);
 
+// Per-z-slice histogram of the interior cells (pdfcalc.jl:13-49): pdf_dev[z * nbins + bin], nbins <= 8192.
+cudaError_t launch_pdf(int dtype, const void* f, const Layout& L, int nbins, double vmin, double vmax,
+                       unsigned* pdf_dev, cudaStream_t st);
+
 // Field statistics over interior cells: out[0]=sum out[1]=sum of squares out[2]=min out[3]=max
 // out[4]=count(value > thresh).  `partials` is device scratch of stats_scratch_doubles() doubles;
 // `out_dev` 5 doubles on the device.

@@ -570,6 +570,42 @@ extern "C" int gsb_field_stats(gsb_t* h, int which, double thresh, double out[5]
     return 0;
 }
 
+// _compute_pdf of src/analysis/pdfcalc.jl:13-49 on the resident field
+extern "C" int gsb_pdf(gsb_t* h, int which, int nbins, double vmin, double vmax, uint32_t* pdf_host, double* bins_host) {
+    if (!h || !pdf_host) return fail("gsb_pdf: null argument");
+    if (which < 0 || which > 3) return fail("gsb_pdf: which = %d", which);
+    if (nbins < 1 || nbins > 8192) return fail("gsb_pdf: nbins = %d outside [1, 8192]", nbins);
+    if (!(vmax >= vmin)) return fail("gsb_pdf: max < min");
+    const size_t n = (size_t)nbins * (size_t)h->L.sz;
+    if (bins_host) {
+        // bins[i] = min + i * bin_width, evaluated in T like the reference
+        if (h->cfg.dtype == GSB_F32) {
+            const float lo = (float)vmin, w = ((float)vmax - lo) / (float)nbins;
+            for (int i = 0; i < nbins; ++i) bins_host[i] = (double)(lo + (float)i * w);
+        } else {
+            const double w = (vmax - vmin) / (double)nbins;
+            for (int i = 0; i < nbins; ++i) bins_host[i] = vmin + (double)i * w;
+        }
+    }
+    // special case of the reference: one bin or an empty window -> every slice holds slice_size
+    const double width = (vmax - vmin) / nbins;
+    if (nbins == 1 || (vmax - vmin) < 1.0e-20 || width < 1.0e-20) {
+        for (size_t i = 0; i < n; ++i) pdf_host[i] = (uint32_t)((size_t)h->L.sx * h->L.sy);
+        return 0;
+    }
+    DeviceGuard guard_(h->device);
+    if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
+    unsigned* dev = nullptr;
+    CK(cudaStreamSynchronize(h->s_comm));
+    CK(cudaMallocAsync((void**)&dev, n * sizeof(unsigned), h->s_compute));
+    cudaError_t e = launch_pdf(h->cfg.dtype, h->f[which], h->L, nbins, vmin, vmax, dev, h->s_compute);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(pdf_host, dev, n * sizeof(unsigned), cudaMemcpyDeviceToHost, h->s_compute);
+    cudaFreeAsync(dev, h->s_compute);
+    if (e != cudaSuccess) return fail("gsb_pdf: %s", cudaGetErrorString(e));
+    CK(cudaStreamSynchronize(h->s_compute));
+    return 0;
+}
+
 // ------------------------------------------------------------------ kernel selection, timers
 extern "C" int gsb_set_kernel(gsb_t* h, int kind, int ty, int stages, int zchunk) {
     if (!h) return fail("null handle");

@@ -159,6 +159,13 @@ class Fields:
         return dict(sum=out[0], sumsq=out[1], min=out[2], max=out[3], count_above=out[4], mean=mean,
                     var=out[1] / n - mean * mean, n=n)
 
+    def pdf(self, slot: int, nbins: int, vmin: float, vmax: float):
+        """_compute_pdf (src/analysis/pdfcalc.jl:13-49): (pdf[sz, nbins] counts, bins[nbins])."""
+        pdf = np.empty((self.sizes[2], nbins), np.uint32)
+        bins = np.empty(nbins, np.float64)
+        check(lib().gsb_pdf(self._h, slot, nbins, vmin, vmax, pdf.ctypes.data, bins.ctypes.data))
+        return pdf, bins
+
     def set_kernel(self, kind=-1, ty=0, stages=0, zchunk=0):
         check(lib().gsb_set_kernel(self._h, kind, ty, stages, zchunk))
 

@@ -168,6 +168,14 @@ int gsb_set_step(gsb_t* h, int64_t step);
  * `which` (out[0..4]); deterministic.  For the statistical noise checks at full size. */
 int gsb_field_stats(gsb_t* h, int which, double thresh, double out[5]);
 
+/* _compute_pdf(data, shape, count, nbins, min, max)  src/analysis/pdfcalc.jl:13-49 (unfinished in the
+ * reference: no return, 0-based bin into a 1-based array): for every z slice of field `which` the
+ * number of interior cells per bin, nbins equal bins over [min, max], bin = floor((value - min) /
+ * bin_width) evaluated in T, value == max in the last bin, values outside the window not counted;
+ * nbins == 1 or a window narrower than 1e-20 gives slice_size everywhere, like the reference.
+ * pdf_host: nbins * sz counts, bin fastest; bins_host (optional): the nbins lower bin edges. */
+int gsb_pdf(gsb_t* h, int which, int nbins, double min, double max, uint32_t* pdf_host, double* bins_host);
+
 /* ---- communication set-up (replaces MPI.Init / Cart_create for the device side) -------- */
 
 /* NCCL transport, one process per GPU: rank 0 obtains the 128-byte id, the caller broadcasts it

@@ -9,7 +9,7 @@ int main(void) {
         (void*)gsb_fill_domain, (void*)gsb_init_fields, (void*)gsb_exchange, (void*)gsb_calculate, (void*)gsb_swap,
         (void*)gsb_step, (void*)gsb_step_group, (void*)gsb_get_fields, (void*)gsb_get_fields_async,
         (void*)gsb_output_wait, (void*)gsb_get_ghosted, (void*)gsb_set_ghosted, (void*)gsb_alloc_host,
-        (void*)gsb_free_host, (void*)gsb_sync, (void*)gsb_get_step, (void*)gsb_set_step, (void*)gsb_field_stats,
+        (void*)gsb_free_host, (void*)gsb_sync, (void*)gsb_get_step, (void*)gsb_set_step, (void*)gsb_field_stats, (void*)gsb_pdf,
         (void*)gsb_get_unique_id, (void*)gsb_comm_init, (void*)gsb_comm_init_local, (void*)gsb_set_kernel,
         (void*)gsb_get_kernel, (void*)gsb_timers_enable, (void*)gsb_timers, (void*)gsb_halo_bytes,
         (void*)gsb_launch_count, (void*)gsb_compute_stream, (void*)gsb_calculate_arrays,

@@ -288,6 +288,32 @@ def test_async_output_equals_blocking_get_fields(sim):
     f.close()
 
 
+@pytest.mark.parametrize("prec", ["Float32", "Float64"])
+def test_pdf_per_slice_histogram(sim, prec):
+    """_compute_pdf of src/analysis/pdfcalc.jl:13-49 (as intended: the reference version is unfinished)
+    against a numpy restatement evaluated in T."""
+    T = np.float32 if prec == "Float32" else np.float64
+    s, mcd, f = make(sim, 48, prec, noise=0.1)
+    sim.iterate(f, s, mcd, nsteps=60)
+    u, v = sim.get_fields(f)
+    for slot, a, (lo, hi), nbins in ((0, u, (0.0, 1.2), 100), (1, v, (0.0, 0.5), 1000), (1, v, (0.05, 0.2), 7)):
+        pdf, bins = f.pdf(slot, nbins, lo, hi)
+        lo_t, hi_t = T(lo), T(hi)
+        w = (hi_t - lo_t) / T(nbins)
+        want = np.zeros((48, nbins), np.uint32)
+        for z in range(48):
+            x = a[z].ravel()
+            x = x[(x >= lo_t) & (x <= hi_t)]
+            b = np.floor((x - lo_t) / w).astype(np.int64)
+            b[b >= nbins] = nbins - 1
+            want[z] = np.bincount(b, minlength=nbins)
+        assert np.array_equal(pdf, want)
+        assert np.array_equal(bins, (lo_t + np.arange(nbins).astype(T) * w).astype(np.float64))
+    one, _ = f.pdf(0, 1, 0.0, 1.0)
+    assert (one == 48 * 48).all()                       # special case of the reference: slice_size
+    f.close()
+
+
 def test_errors(sim):
     with pytest.raises(sim.GsbError, match="odd"):
         make(sim, 7, "Float32")                         # Int64(L/2 - 6): InexactError in the reference

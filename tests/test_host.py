@@ -38,7 +38,7 @@ def test_header_is_valid_c_and_links(pkg, tmp_path):
     assert r.returncode == 0, r.stderr
     r = subprocess.run([str(exe)], capture_output=True, text=True)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
-    assert "35 symbols, version 100" in r.stdout
+    assert "36 symbols, version 100" in r.stdout
     # the Python mirror of struct gsb_config has the same size as the C one
     assert f"sizeof(gsb_config) = {C.sizeof(pkg._lib.GsbConfig)}" in r.stdout
 
