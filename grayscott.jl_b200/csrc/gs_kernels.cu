@@ -1,4 +1,4 @@
-// gs_kernels.cu -- auxiliary kernels (init, layout conversion, halo pack/unpack, statistics),
+// gs_kernels.cu -- auxiliary kernels (init, halo pack/unpack, per-slice PDF, statistics),
 // the TMA tensor-map encoder and the dtype dispatch of the stencil launchers.
 #include <cfloat>
 #include <cstdio>

@@ -334,7 +334,7 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
                         (long long)h->global[d]);
         if (c.offsets[d] < 0 || c.offsets[d] + c.sizes[d] > h->global[d])
             return fail("offsets[%d] + sizes[%d] exceeds the global extent", d, d);
-        if (h->global[d] >= (1ll << 32)) return fail("global extent too large for the 32-bit noise counter");
+        if (h->global[d] >= (1ll << 31)) return fail("global extent too large for the 32-bit cell coordinates of the noise counter");
     }
     h->es = c.dtype == GSB_F32 ? 4 : 8;
     h->device = c.device;
