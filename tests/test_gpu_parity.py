@@ -521,3 +521,27 @@ def test_full_size_L1024_matches_small_grid_in_the_domain_of_dependence(sim, orc
     far[:, :n + 1] = far[:, -n - 1:] = False
     far[:, :, :n + 1] = far[:, :, -n - 1:] = False
     assert (u[far] == 1).all() and (v[far] == 0).all()
+
+
+def test_full_size_L1024_noise_statistics(sim, orc):
+    """BASELINE config 3 with noise = 0.1 (the headline bench workload), native Float32 arithmetic.  The
+    fields are far too large to compare cell by cell with the CPU solver, but away from the tiny
+    initial block the update is a linear stochastic recursion whose moments do not depend on L: mean and
+    variance of u and v after n steps must match a small grid run by the oracle with xoshiro noise (the
+    reference's kind of generator), to sampling accuracy; computed on the device (no 8 GB download)."""
+    n = 6
+    s, mcd, f = make(sim, 1024, "Float32", noise=0.1, arith=NATIVE)
+    sim.iterate(f, s, mcd, nsteps=n)
+    su, sv = f.stats(0, 0.5), f.stats(1, 0.1)
+    f.close()
+    o = orc.Oracle(128, "Float32", noise=0.1, noise_mode=orc.NOISE_XOSHIRO, seed=77, **PHYS)
+    o.step(n)
+    uo, vo = (a.astype(np.float64) for a in o.get_fields())
+    # reference region: a corner block of the small grid that neither the boundary layer (8 cells) nor
+    # the initial block's neighbourhood (n cells around the centre) has reached -- pure noise statistics
+    far = (slice(8, 40),) * 3
+    assert abs(su["mean"] - uo[far].mean()) < 2e-3
+    assert abs(su["var"] - uo[far].var()) < 0.05 * uo[far].var()
+    # v is non-zero only around the initial block: its total mass does not depend on L
+    assert abs(sv["sum"] - vo.sum()) < 0.03 * vo.sum()
+    assert su["min"] > -0.5 and su["max"] < 2.0 and sv["min"] >= -1e-3
