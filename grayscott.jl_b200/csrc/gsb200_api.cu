@@ -910,7 +910,7 @@ static int enqueue_exchange_now(gsb_handle* h, bool local_second_half) {
 static int pipeline_chunks(const gsb_handle* h) {
     if (!h->n_active) return 1;
     const int sz = h->L.sz;
-    int c = h->halo_chunks > 0 ? h->halo_chunks : (sz >= 512 ? 4 : sz >= 192 ? 3 : sz >= 32 ? 2 : 1);
+    int c = h->halo_chunks > 0 ? h->halo_chunks : (sz >= 192 ? 4 : sz >= 32 ? 2 : 1);
     if (c > GSB_MAX_CHUNKS) c = GSB_MAX_CHUNKS;
     if (c > sz) c = sz;
     return c < 1 ? 1 : c;
