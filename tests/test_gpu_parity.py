@@ -105,11 +105,11 @@ def test_native_f32_within_tolerance_L64_1000(sim, orc):
 
 @pytest.mark.parametrize("prec,arith", [("Float32", REFERENCE), ("Float32", NATIVE), ("Float64", REFERENCE)])
 def test_config2_L256(sim, orc, prec, arith):
-    """BASELINE config 2: L = 256, noise = 0, one B200 vs the reference CPU solver, N = 1, 10, 100."""
+    """BASELINE config 2: L = 256, noise = 0, one B200 vs the reference CPU solver, N = 1, 10, 100, 1000."""
     s, mcd, f = make(sim, 256, prec, arith=arith)
     o = orc.Oracle(256, prec, **PHYS)
     done = 0
-    for n in (1, 10, 100):
+    for n in (1, 10, 100, 1000):
         sim.iterate(f, s, mcd, nsteps=n - done)
         o.step(n - done)
         done = n
