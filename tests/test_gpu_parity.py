@@ -25,6 +25,22 @@ def rel_err(a, b):
     return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max() / max(np.abs(b).max(), 1e-300))
 
 
+def ks_distance(a, b):
+    a, b = np.sort(a.ravel().astype(np.float64)), np.sort(b.ravel().astype(np.float64))
+    allv = np.concatenate([a, b])
+    return float(np.abs(np.searchsorted(a, allv, side="right") / a.size - np.searchsorted(b, allv, side="right") / b.size).max())
+
+
+def radial_profile(a, nbins=24):
+    """Mean of the field in shells about the grid centre; returns (profile, cells per shell)."""
+    L = a.shape[0]
+    z, y, x = np.indices(a.shape)
+    r = np.sqrt((x - L / 2 + 0.5) ** 2 + (y - L / 2 + 0.5) ** 2 + (z - L / 2 + 0.5) ** 2)
+    idx = np.minimum((r / (L / 2) * nbins).astype(int), nbins - 1).ravel()
+    cnt = np.bincount(idx, minlength=nbins)
+    return np.bincount(idx, a.ravel().astype(np.float64), nbins) / np.maximum(cnt, 1), cnt
+
+
 def settings(sim, L, prec, noise=0.0, phys=PHYS):
     return sim.Settings(L=L, precision=prec, backend="B200", kernel_language="Plain", noise=noise, **phys)
 
@@ -223,6 +239,14 @@ def test_noise_run_config1(sim, orc, prec):
         assert abs(x.min() - y.min()) < 0.1 and abs(x.max() - y.max()) < 0.1
     area, area_b = (v > 0.1).mean(), (vb > 0.1).mean()
     assert abs(area - area_b) < 0.02
+    # distribution of values (Kolmogorov-Smirnov distance) and radial profile about the centre;
+    # two independent noise realisations of the oracle differ by <= 0.005 / 0.003 / 0.035 here
+    for x, y in ((u, ub), (v, vb)):
+        assert ks_distance(x, y) < 0.02
+        pa, cnt = radial_profile(x)
+        pb, _ = radial_profile(y)
+        assert (np.abs(pa - pb) * cnt).sum() / cnt.sum() < 0.01
+        assert np.abs(pa - pb)[4:].max() < 0.08
     # on-device statistics agree with numpy
     st = f.stats(1, 0.1)
     assert st["count_above"] == float((v > 0.1).sum())
