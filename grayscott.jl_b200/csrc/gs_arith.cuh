@@ -35,6 +35,17 @@ __device__ __forceinline__ double noise_term(const Params& p, double ri) {
     return p.noise_fast ? __dmul_rn(p.noise_s, ri) : __dmul_rn(p.noise, __dmul_rn(ri, 0x1.0p-31));
 }
 
+// Same quotient when x is an exact difference of Float32-derived values (the Float32 fields): such an
+// x is either zero or at least 2^-149 in magnitude, so no intermediate can underflow and only the sign
+// of a zero quotient needs care (+-0 / 6 = +-0).
+__device__ __forceinline__ double div6_rn_f32src(double x) {
+    const double c = 0x1.5555555555555p-3;
+    const double q = __dmul_rn(x, c);
+    const double r = __fma_rn(-6.0, q, x);
+    const double res = __fma_rn(r, c, q);
+    return x == 0.0 ? x : res;
+}
+
 // su, sv: the left-folded six-neighbour sums ((((W+E)+S)+N)+D)+U computed in T by the caller.
 // r: integer-valued noise variate ri in [-2^31, 2^31) (reference) / r32 in [-1,1) (native); ignored
 // unless NOISE.
@@ -44,8 +55,8 @@ __device__ __forceinline__ void cell_update_ref(float uc, float vc, float su, fl
                                                 const Params& p, float& un, float& vn) {
     const double u64 = (double)uc, v64 = (double)vc;
     // (Float64(su) - 6.0*Float64(uc)) / 6.0 ; 6.0*uc is exact in Float64, so one FMA == mul, sub
-    const double lap_u = div6_rn(__fma_rn(-6.0, u64, (double)su));
-    const double lap_v = div6_rn(__fma_rn(-6.0, v64, (double)sv));
+    const double lap_u = div6_rn_f32src(__fma_rn(-6.0, u64, (double)su));
+    const double lap_v = div6_rn_f32src(__fma_rn(-6.0, v64, (double)sv));
     const float uvv = __fmul_rn(uc, __fmul_rn(vc, vc));            // u * v^2       (Float32)
     const float fkv = __fmul_rn(p.fFK, vc);                        // (F + K) * v   (Float32)
     double du = __dsub_rn(__dmul_rn(p.Du, lap_u), (double)uvv);
