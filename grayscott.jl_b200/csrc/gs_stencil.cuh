@@ -183,8 +183,8 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsi
                                             const Vec<T>& b0, Vec<T>& bp, const int roff, const int eoff,
                                             const bool lane_w, const bool lane_e, const bool vec_active,
                                             const Params& p, const Box& box, const int x, const int y, const int z,
-                                            T*& pou, T*& pov, const long long pxy, const bool ghost_ext, const T gu,
-                                            const T gv, T* sdst, const int sidx, const int svoff) {
+                                            T*& pou, T*& pov, const long long pxy, const bool own_x, const T gu,
+                                            const T gv, T* sp, const int svoff) {
     using Tile = TmaTile<T, TY>;
     constexpr int N = Tile::N;
     const T* su_ = reinterpret_cast<const T*>(cur);
@@ -198,7 +198,7 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsi
         const Vec<T> vs = ld_vec(pv_ + roff - Tile::BW), vn = ld_vec(pv_ + roff + Tile::BW);
         // x neighbours across vectors: shuffles inside the warp, the box halo for lanes 0 and 31
         T eu = T(0), ev = T(0);
-        if (XF && ghost_ext) { eu = gu; ev = gv; }                 // ghost from the dense receive buffer
+        if (XF && own_x) { eu = gu; ev = gv; }                     // ghost from the dense receive buffer
         else if (lane_w || lane_e) { eu = pu_[eoff]; ev = pv_[eoff]; }
         const T su = __shfl_up_sync(0xffffffffu, a0.a[N - 1], 1), sd = __shfl_down_sync(0xffffffffu, a0.a[0], 1);
         const T tu = __shfl_up_sync(0xffffffffu, b0.a[N - 1], 1), td = __shfl_down_sync(0xffffffffu, b0.a[0], 1);
@@ -210,9 +210,9 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsi
             store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
             pou += pxy;
             pov += pxy;
-            if (XF && sdst) {                                      // my boundary column goes out with the update
-                sdst[sidx] = lane_w ? ou.a[0] : ou.a[N - 1];
-                sdst[svoff + sidx] = lane_w ? ov.a[0] : ov.a[N - 1];
+            if (XF && own_x) {                                     // my boundary column goes out with the update
+                sp[0] = lane_w ? ou.a[0] : ou.a[N - 1];
+                sp[svoff] = lane_w ? ov.a[0] : ov.a[N - 1];
             }
         }
     }
@@ -288,31 +288,34 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
 #pragma unroll
     for (int q = 0; q < N; ++q) { ua.a[q] = ub.a[q] = uc.a[q] = va.a[q] = vb.a[q] = vc.a[q] = T(0); }
 
-    // x faces carried by this kernel (XFaceArgs): only the lane owning column 0 / sx-1 takes part
-    const bool own_lo = lane_w && xtile == 0, own_hi = lane_e && xtile + 32 * N == L.sx;
-    const T* gsrc = (XF && row_active) ? (own_lo ? (const T*)xf.ghost_lo : own_hi ? (const T*)xf.ghost_hi : nullptr) : nullptr;
-    T* sdst = (XF && vec_active) ? (own_lo ? (T*)xf.send_lo : own_hi ? (T*)xf.send_hi : nullptr) : nullptr;
-    const int svoff = L.sy * xf.nz;                          // a face piece has < 2^31 elements
-    const int fidx0 = y + L.sy * (zs - xf.zbase);            // face element of plane zs
-    // three rotating ghost pairs: the pair loaded in one iteration is consumed in the next without a
-    // register move (a move would wait for the load on the spot)
-    T g0u = T(0), g0v = T(0), g1u = T(0), g1v = T(0), g2u = T(0), g2v = T(0);
+    // x faces carried by this kernel (XFaceArgs; ghost_* and send_* are set together): only the lane
+    // that owns column 0 / sx-1 of an active row takes part.  gp walks the receive piece one plane per
+    // iteration, the matching element of the message being built is gp + sdelta.
+    const bool own_lo = lane_w && xtile == 0 && xf.ghost_lo != nullptr;
+    const bool own_hi = lane_e && xtile + 32 * N == L.sx && xf.ghost_hi != nullptr;
+    const bool own_x = XF && vec_active && (own_lo || own_hi);
+    const int svoff = L.sy * xf.nz;                          // v part of a piece; a piece has < 2^31 elements
+    // element of (y, plane zs) in a piece; addresses are rebuilt from it every iteration instead of
+    // carrying pointers in registers (the plain kernel already sits at its register cap)
+    const int fidx0 = y + L.sy * (zs - xf.zbase);
+    T gu = T(0), gv = T(0);
 
     int s = 0, sprev = 0;
     unsigned ph = 0;
-    // one step of the ring: wait for plane i, consume, release the slot of plane i-1
-#define GSB_TMA_STEP(AM, A0, AP, BM, B0, BP, GCU, GCV, GNU, GNV)                                          \
+    // one step of the ring: wait for plane i, consume (plane i-1 is updated), fetch the x ghost the
+    // next iteration needs into the registers the consume has just finished with, release plane i-1
+#define GSB_TMA_STEP(AM, A0, AP, BM, B0, BP)                                                              \
     {                                                                                                     \
-        if (XF && gsrc && i >= 1 && i - 1 < ze - zs) { /* ghost of the plane computed in the NEXT iteration */ \
-            const int e = fidx0 + L.sy * (i - 1);                                                         \
-            GNU = gsrc[e];                                                                                \
-            GNV = gsrc[svoff + e];                                                                        \
-        }                                                                                                 \
         mbar_wait(full_bar(s), ph);                                                                       \
         tma_consume<T, ARITH, NOISE, TY, XF>(tiles + s * Tile::STAGE_BYTES, tiles + sprev * Tile::STAGE_BYTES, i, \
                                          AM, A0, AP, BM, B0, BP, roff, eoff, lane_w, lane_e, vec_active, p, box, x, \
-                                         y, zs + i - 2, pou, pov, L.pxy, XF && gsrc != nullptr, GCU, GCV, sdst, \
-                                         fidx0 + L.sy * (i - 2), svoff);                                  \
+                                         y, zs + i - 2, pou, pov, L.pxy, own_x, gu, gv,                   \
+                                         (own_lo ? (T*)xf.send_lo : (T*)xf.send_hi) + (fidx0 + L.sy * (i - 2)), svoff); \
+        if (XF && own_x && (unsigned)(i - 1) < (unsigned)(ze - zs)) {                                     \
+            const T* gp = (own_lo ? (const T*)xf.ghost_lo : (const T*)xf.ghost_hi) + (fidx0 + L.sy * (i - 1)); \
+            gu = gp[0];                                 /* ghost of plane zs + i - 1, used next iteration */ \
+            gv = gp[svoff];                                                                               \
+        }                                                                                                 \
         if (i >= 1) {                                                                                     \
             __syncwarp();                                                                                 \
             if (lane == 0) mbar_arrive(empty_bar(sprev));                                                 \
@@ -323,13 +326,13 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
     }
     int i = 0;
     while (i + 3 <= nplanes) {
-        GSB_TMA_STEP(ua, ub, uc, va, vb, vc, g0u, g0v, g1u, g1v)
-        GSB_TMA_STEP(ub, uc, ua, vb, vc, va, g1u, g1v, g2u, g2v)
-        GSB_TMA_STEP(uc, ua, ub, vc, va, vb, g2u, g2v, g0u, g0v)
+        GSB_TMA_STEP(ua, ub, uc, va, vb, vc)
+        GSB_TMA_STEP(ub, uc, ua, vb, vc, va)
+        GSB_TMA_STEP(uc, ua, ub, vc, va, vb)
     }
     if (i < nplanes) {
-        GSB_TMA_STEP(ua, ub, uc, va, vb, vc, g0u, g0v, g1u, g1v)
-        if (i < nplanes) GSB_TMA_STEP(ub, uc, ua, vb, vc, va, g1u, g1v, g2u, g2v)
+        GSB_TMA_STEP(ua, ub, uc, va, vb, vc)
+        if (i < nplanes) GSB_TMA_STEP(ub, uc, ua, vb, vc, va)
     }
 #undef GSB_TMA_STEP
 }

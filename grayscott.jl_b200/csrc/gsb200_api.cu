@@ -765,8 +765,9 @@ static bool interior_box(const gsb_handle* h, Box* b) {
 // Optional ($GSB_FUSE_X=1 at gsb_create): the x faces ride inside the update kernel (XFaceArgs) when the
 // pipelined scheme runs the TMA kernel on a subdomain whose sx is a whole number of tiles.  It removes
 // the strided pack/unpack of 2 * sy * sz cells (~0.1 ms per step at 1024^3), but the XF instantiation
-// of the kernel currently executes ~40 % more instructions and loses more than that (measured
-// 3.7 vs 3.1 ms per step), so it is OFF by default; kept because it is bit-exact and tested.
+// of the kernel runs against the register cap (spills, re-materialised indices) and loses more than
+// that (measured per step, two subdomains of 1024^3: 3.21 vs 3.05 ms without noise, 3.62 vs 3.18 ms
+// with), so it is OFF by default; kept because it is bit-exact and tested.
 static bool fused_x(const gsb_handle* h) {
     const int tile = 32 * (int)(16 / h->es);
     return h->fuse_x && h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
