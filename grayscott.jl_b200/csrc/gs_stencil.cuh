@@ -177,7 +177,7 @@ struct TmaTile {
 // One consumer iteration: plane index i of the chunk has landed in slot `cur`; am/a0 (bm/b0) hold
 // the centre vectors of planes i-2 / i-1, ap (bp) receives plane i; plane i-1 sits in slot `prev`.
 // The caller rotates the register names (three-way unrolled loop), so no register moves.
-template <typename T, int ARITH, bool NOISE, int TY, bool XF>
+template <typename T, int ARITH, bool NOISE, int TY, int XF>
 __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsigned char* prev, int i,
                                             const Vec<T>& am, const Vec<T>& a0, Vec<T>& ap, const Vec<T>& bm,
                                             const Vec<T>& b0, Vec<T>& bp, const int roff, const int eoff,
@@ -198,7 +198,7 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsi
         const Vec<T> vs = ld_vec(pv_ + roff - Tile::BW), vn = ld_vec(pv_ + roff + Tile::BW);
         // x neighbours across vectors: shuffles inside the warp, the box halo for lanes 0 and 31
         T eu = T(0), ev = T(0);
-        if (XF && own_x) { eu = gu; ev = gv; }                     // ghost from the dense receive buffer
+        if (XF == 2 && own_x) { eu = gu; ev = gv; }                // ghost from the dense receive buffer
         else if (lane_w || lane_e) { eu = pu_[eoff]; ev = pv_[eoff]; }
         const T su = __shfl_up_sync(0xffffffffu, a0.a[N - 1], 1), sd = __shfl_down_sync(0xffffffffu, a0.a[0], 1);
         const T tu = __shfl_up_sync(0xffffffffu, b0.a[N - 1], 1), td = __shfl_down_sync(0xffffffffu, b0.a[0], 1);
@@ -210,7 +210,7 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsi
             store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
             pou += pxy;
             pov += pxy;
-            if (XF && own_x) {                                     // my boundary column goes out with the update
+            if (XF >= 1 && own_x) {                                // my boundary column goes out with the update
                 sp[0] = lane_w ? ou.a[0] : ou.a[N - 1];
                 sp[svoff] = lane_w ? ov.a[0] : ov.a[N - 1];
             }
@@ -218,9 +218,11 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsi
     }
 }
 
-// XF: this instantiation carries the x faces itself (XFaceArgs); kept apart so that the plain
-// kernel pays neither the registers nor the instructions.
-template <typename T, int ARITH, bool NOISE, int TY, int STAGES, int MINB, bool XF>
+// XF: how much of the x faces this instantiation carries itself (XFaceArgs): 0 nothing, 1 it writes
+// its boundary columns into the message buffers (no strided pack), 2 it also reads its x ghosts from
+// the receive buffers (no strided unpack).  Kept apart so that the plain kernel pays neither the
+// registers nor the instructions.
+template <typename T, int ARITH, bool NOISE, int TY, int STAGES, int MINB, int XF>
 __global__ void __launch_bounds__(32 * (TY + 1), MINB)
 stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_v,
                    T* __restrict__ uo, T* __restrict__ vo, const Layout L, const Params p, const Box box,
@@ -288,12 +290,11 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
 #pragma unroll
     for (int q = 0; q < N; ++q) { ua.a[q] = ub.a[q] = uc.a[q] = va.a[q] = vb.a[q] = vc.a[q] = T(0); }
 
-    // x faces carried by this kernel (XFaceArgs; ghost_* and send_* are set together): only the lane
-    // that owns column 0 / sx-1 of an active row takes part.  gp walks the receive piece one plane per
-    // iteration, the matching element of the message being built is gp + sdelta.
-    const bool own_lo = lane_w && xtile == 0 && xf.ghost_lo != nullptr;
-    const bool own_hi = lane_e && xtile + 32 * N == L.sx && xf.ghost_hi != nullptr;
-    const bool own_x = XF && vec_active && (own_lo || own_hi);
+    // x faces carried by this kernel (XFaceArgs; send_* set, ghost_* set too when XF == 2): only the
+    // lane that owns column 0 / sx-1 of an active row takes part
+    const bool own_lo = lane_w && xtile == 0 && xf.send_lo != nullptr;
+    const bool own_hi = lane_e && xtile + 32 * N == L.sx && xf.send_hi != nullptr;
+    const bool own_x = XF >= 1 && vec_active && (own_lo || own_hi);
     const int svoff = L.sy * xf.nz;                          // v part of a piece; a piece has < 2^31 elements
     // element of (y, plane zs) in a piece; addresses are rebuilt from it every iteration instead of
     // carrying pointers in registers (the plain kernel already sits at its register cap)
@@ -311,7 +312,7 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
                                          AM, A0, AP, BM, B0, BP, roff, eoff, lane_w, lane_e, vec_active, p, box, x, \
                                          y, zs + i - 2, pou, pov, L.pxy, own_x, gu, gv,                   \
                                          (own_lo ? (T*)xf.send_lo : (T*)xf.send_hi) + (fidx0 + L.sy * (i - 2)), svoff); \
-        if (XF && own_x && (unsigned)(i - 1) < (unsigned)(ze - zs)) {                                     \
+        if (XF == 2 && own_x && (unsigned)(i - 1) < (unsigned)(ze - zs)) {                                \
             const T* gp = (own_lo ? (const T*)xf.ghost_lo : (const T*)xf.ghost_hi) + (fidx0 + L.sy * (i - 1)); \
             gu = gp[0];                                 /* ghost of plane zs + i - 1, used next iteration */ \
             gv = gp[svoff];                                                                               \

@@ -762,16 +762,19 @@ static bool interior_box(const gsb_handle* h, Box* b) {
     return true;
 }
 
-// Optional ($GSB_FUSE_X=1 at gsb_create): the x faces ride inside the update kernel (XFaceArgs) when the
+// Optional ($GSB_FUSE_X=1|2 at gsb_create): the x faces ride inside the update kernel (XFaceArgs) when the
 // pipelined scheme runs the TMA kernel on a subdomain whose sx is a whole number of tiles.  It removes
 // the strided pack/unpack of 2 * sy * sz cells (~0.1 ms per step at 1024^3), but the XF instantiation
 // of the kernel runs against the register cap (spills, re-materialised indices) and loses more than
 // that (measured per step, two subdomains of 1024^3: 3.21 vs 3.05 ms without noise, 3.62 vs 3.18 ms
 // with), so it is OFF by default; kept because it is bit-exact and tested.
-static bool fused_x(const gsb_handle* h) {
+// Returns 0 (off), 1 (the kernel writes the x messages: no strided pack) or 2 (it also reads the x ghosts
+// from the receive buffers: no strided unpack).
+static int fused_x(const gsb_handle* h) {
     const int tile = 32 * (int)(16 / h->es);
-    return h->fuse_x && h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
-           (h->active[GSB_WEST] || h->active[GSB_EAST]) && h->L.sx % tile == 0;
+    const bool can = h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
+                     (h->active[GSB_WEST] || h->active[GSB_EAST]) && h->L.sx % tile == 0;
+    return can ? (h->fuse_x >= 2 ? 2 : h->fuse_x == 1 ? 1 : 0) : 0;
 }
 
 // A piece of the halo: which faces travel, and for the x / y faces which z range.
@@ -950,11 +953,11 @@ static XFaceArgs chunk_xface(const gsb_handle* h, int k, int C) {
     const int rd = (int)(h->step & 1), wr = (int)((h->step + 1) & 1);
     auto at = [&](void* base, int d) { return (void*)((char*)base + piece_offset(h, d, pc.z0)); };
     if (h->active[GSB_WEST]) {
-        xf.ghost_lo = at(h->recv[rd][GSB_WEST], GSB_WEST);
+        if (fused_x(h) == 2) xf.ghost_lo = at(h->recv[rd][GSB_WEST], GSB_WEST);
         xf.send_lo = at(h->transport == TR_LOCAL ? h->peer[GSB_WEST]->recv[wr][GSB_EAST] : h->send[GSB_WEST], GSB_WEST);
     }
     if (h->active[GSB_EAST]) {
-        xf.ghost_hi = at(h->recv[rd][GSB_EAST], GSB_EAST);
+        if (fused_x(h) == 2) xf.ghost_hi = at(h->recv[rd][GSB_EAST], GSB_EAST);
         xf.send_hi = at(h->transport == TR_LOCAL ? h->peer[GSB_EAST]->recv[wr][GSB_WEST] : h->send[GSB_EAST], GSB_EAST);
     }
     return xf;
@@ -1014,7 +1017,7 @@ static int pipeline_prime(gsb_handle** hs, int n) {
         for (int r = 0; r < n; ++r) {
             gsb_handle* h = hs[r];
             if (h->n_active)
-                if (enqueue_unpack(h, chunk_piece(h, k, C), 0, (int)(h->step & 1), h->ev_piece[k], fused_x(h))) return 1;
+                if (enqueue_unpack(h, chunk_piece(h, k, C), 0, (int)(h->step & 1), h->ev_piece[k], fused_x(h) == 2)) return 1;
         }
     }
     for (int r = 0; r < n; ++r) if (hs[r]->n_active) {
@@ -1029,7 +1032,7 @@ static int pipeline_prime(gsb_handle** hs, int n) {
 // Array(fields.u) must show the neighbours' columns although, in the fused scheme, the kernels read
 // them from the receive buffers: copy them into the ghost columns of the current fields on demand.
 static int refresh_x_ghosts(gsb_handle* h) {
-    if (!h->n_active || !h->ghost_valid || !fused_x(h)) return 0;
+    if (!h->n_active || !h->ghost_valid || fused_x(h) != 2) return 0;
     const int C = pipeline_chunks(h);
     for (int k = 0; k < C; ++k) {
         Piece pc = chunk_piece(h, k, C);
@@ -1063,12 +1066,12 @@ static int pipeline_step(gsb_handle** hs, int n) {
             gsb_handle* h = hs[r];
             if (pipeline_compute_chunk(h, k, C, ps[r], i)) return 1;
             if (h->n_active)
-                if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk, fused_x(h))) return 1;
+                if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk, fused_x(h) >= 1)) return 1;
         }
         for (int r = 0; r < n; ++r) {
             gsb_handle* h = hs[r];
             if (h->n_active)
-                if (enqueue_unpack(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_piece[k], fused_x(h))) return 1;
+                if (enqueue_unpack(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_piece[k], fused_x(h) == 2)) return 1;
         }
     }
     for (int r = 0; r < n; ++r) { swap_bindings(hs[r]); hs[r]->ghost_valid = hs[r]->n_active > 0; }

@@ -451,13 +451,14 @@ def test_halo_exchange_other_decompositions(sim, orc, monkeypatch, nranks, L, sc
 @pytest.mark.parametrize("prec", ["Float32", "Float64"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
 @pytest.mark.parametrize("chunks", [None, 1, 3])
-def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nranks, chunks):
-    """Optional scheme (GSB_FUSE_X=1): sx = 128 is a whole number of tiles, so the update kernel can
-    write its boundary columns into the message buffers and read its x ghosts from the receive buffers
-    (no strided pack/unpack).  Must equal the oracle's N-rank run bit for bit, and Array(fields.u) must
+@pytest.mark.parametrize("level", [1, 2])
+def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nranks, chunks, level):
+    """Optional scheme (GSB_FUSE_X=1|2): sx = 128 is a whole number of tiles, so the update kernel can
+    write its boundary columns into the message buffers (level 1: no strided pack) and also read its x
+    ghosts from the receive buffers (level 2: no strided unpack either).  Must equal the oracle's N-rank run bit for bit, and Array(fields.u) must
     still show the neighbour's column in the ghost layer."""
     monkeypatch.setenv("GSB_HALO", "pipeline")
-    monkeypatch.setenv("GSB_FUSE_X", "1")
+    monkeypatch.setenv("GSB_FUSE_X", str(level))
     if chunks:
         monkeypatch.setenv("GSB_HALO_CHUNKS", str(chunks))
     else:
