@@ -194,7 +194,7 @@ def run_reference(a):
         "e2e": {"value": glups, "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(a, n, cpu_sample_L=None):
@@ -425,13 +425,31 @@ def run_b200(a):
             "value": v, "unit": "GLUPS", "cores": thr, "kind": "port",
             "sample": (f"L={Ls} cube, {st} steps in {secs:.1f} s, same physics and noise draw per cell; C restatement of "
                        f"the reference's Julia CPU-threaded solver (Julia unavailable on this box), {thr} OpenMP threads")}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line, on the process's real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     a = parse()
+    # libraries chat on stdout (NCCL prints its version there): keep stdout for the JSON line alone
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:
