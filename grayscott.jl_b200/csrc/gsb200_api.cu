@@ -221,10 +221,20 @@ static void default_kernel(gsb_handle* h) {
         k.kind = KERNEL_TMA_HI; k.ty = 8; k.stages = 4; k.zchunk = 64;
     }
     // small grids: more, smaller CTAs (measured at L = 256: 4 rows per CTA beats 8 by 6 %)
-    if ((long long)h->L.sx * h->L.sy * h->L.sz <= 300ll * 300 * 300 && k.dtype == DT_F32 && k.arith == ARITH_NATIVE) {
+    if ((long long)h->L.sx * h->L.sy * h->L.sz <= 300ll * 300 * 300 && (k.dtype == DT_F64 || k.arith == ARITH_NATIVE)) {
         k.ty = 4; k.stages = 4; k.zchunk = 16;
     }
     const int n = (int)(16 / h->es);
+    const long long cells = (long long)h->L.sx * h->L.sy * h->L.sz;
+    if (cells <= (k.dtype == DT_F64 ? 100ll * 100 * 100 : 140ll * 140 * 140)) {
+        // L2-resident grids are latency-bound: the kernel without the TMA ring, 4 rows per CTA and very
+        // short z chunks so that a few hundred CTAs exist (measured: L = 64 5.1 us per step against 13.3,
+        // L = 128 10.3 against 14.4)
+        k.kind = KERNEL_L1; k.ty = 4; k.stages = 4; k.zchunk = 32;   // (stages: unused by this kernel)
+        const long long t4 = (long long)((h->L.sx + 32 * n - 1) / (32 * n)) * ((h->L.sy + 3) / 4);
+        while (k.zchunk > 2 && t4 * ((h->L.sz + k.zchunk - 1) / k.zchunk) < 512) k.zchunk /= 2;
+        return;
+    }
     const long long tiles = (long long)((h->L.sx + 32 * n - 1) / (32 * n)) * ((h->L.sy + k.ty - 1) / k.ty);
     while (k.zchunk > 8 && tiles * ((h->L.sz + k.zchunk - 1) / k.zchunk) < 148 * 8) k.zchunk /= 2;
 }

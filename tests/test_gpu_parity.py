@@ -427,6 +427,7 @@ def test_halo_exchange_other_decompositions(sim, orc, monkeypatch, nranks, L, sc
     """Decompositions with interior ranks (two neighbours per dimension) and unequal dims:
     3 -> (3,1,1), 6 -> (3,2,1), 12 -> (3,2,2), 27 -> (3,3,3); against the oracle's N-rank run."""
     monkeypatch.setenv("GSB_HALO", scheme[0])
+    monkeypatch.setenv("GSB_KERNEL", "tma:8:4:16")      # small subdomains default to the L1 kernel: keep the TMA one covered
     if scheme[1]:
         monkeypatch.setenv("GSB_HALO_CHUNKS", str(scheme[1]))
     else:
@@ -459,6 +460,7 @@ def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nrank
     still show the neighbour's column in the ghost layer."""
     monkeypatch.setenv("GSB_HALO", "pipeline")
     monkeypatch.setenv("GSB_FUSE_X", str(level))
+    monkeypatch.setenv("GSB_KERNEL", "tma:8:4:16")      # the fused variants exist for the TMA kernel only
     if chunks:
         monkeypatch.setenv("GSB_HALO_CHUNKS", str(chunks))
     else:
