@@ -421,6 +421,31 @@ def test_halo_exchange_bit_exact_vs_single_subdomain(sim, orc, monkeypatch, prec
     one.close()
 
 
+@pytest.mark.parametrize("prec", ["Float32", "Float64"])
+@pytest.mark.parametrize("nranks,L", [(2, 2), (8, 2), (8, 4), (4, 6), (27, 6)])
+@pytest.mark.parametrize("scheme", ["pipeline", "split"])
+def test_halo_exchange_tiny_subdomains(sim, orc, monkeypatch, prec, nranks, L, scheme):
+    """Subdomains of one to a few cells per side (every cell is a boundary cell; with L = 2 on 8 ranks
+    each rank owns a single cell whose six neighbours are all ghosts)."""
+    monkeypatch.setenv("GSB_HALO", scheme)
+    monkeypatch.delenv("GSB_HALO_CHUNKS", raising=False)
+    monkeypatch.delenv("GSB_KERNEL", raising=False)
+    s = settings(sim, L, prec, 0.1, PHYS_DEFAULT)
+    ranks = []
+    for r in range(nranks):
+        mcd = sim.init_domain(s, r, nranks)
+        ranks.append((mcd, sim.init_fields(s, mcd, prec, seed=2)))
+    sim.connect_local([f for _, f in ranks])
+    sim.iterate_group([f for _, f in ranks], s, nsteps=5)
+    o = orc.Oracle(L, prec, dims=orc.dims_create(nranks), noise=0.1, seed=2, **PHYS_DEFAULT)
+    o.step(5)
+    for r, (mcd, f) in enumerate(ranks):
+        u, v = sim.get_fields(f)
+        uo, vo = o.get_fields(r)
+        assert np.array_equal(u, uo) and np.array_equal(v, vo), r
+        f.close()
+
+
 @pytest.mark.parametrize("nranks,L", [(3, 48), (6, 48), (12, 48), (27, 54)])
 @pytest.mark.parametrize("scheme", [("pipeline", None), ("pipeline", 3), ("split", None)])
 def test_halo_exchange_other_decompositions(sim, orc, monkeypatch, nranks, L, scheme):
