@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "../../include/gsb200.h"
@@ -66,7 +67,10 @@ struct NcclApi {
 };
 static NcclApi g_nccl;
 
+static std::mutex g_nccl_mu;
+
 static int nccl_load() {
+    std::lock_guard<std::mutex> lock(g_nccl_mu);
     if (g_nccl.lib) return 0;
     void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
