@@ -51,3 +51,31 @@ def test_nccl_halo_bit_exact_vs_single_gpu(sim, orc, tmp_path, nranks, prec, noi
         o.step(steps)
         uo, vo = o.gather()
         assert np.array_equal(U, uo) and np.array_equal(V, vo)
+
+
+@pytest.mark.parametrize("prec,noise", [("Float32", 0.1), ("Float64", 0.0)])
+@pytest.mark.parametrize("scheme", ["pipeline", "split"])
+def test_inprocess_ranks_on_separate_gpus(sim, orc, monkeypatch, prec, noise, scheme):
+    """gsb_comm_init_local with the handles on DIFFERENT devices of one process: the pack kernel stores
+    straight into the neighbour GPU's receive buffer over NVLink (peer access), events order the two
+    devices.  Must equal the oracle's N-rank run bit for bit."""
+    ndev = n_gpus()
+    if ndev < 2:
+        pytest.skip("needs >= 2 GPUs")
+    monkeypatch.setenv("GSB_HALO", scheme)
+    nranks = 8 if ndev >= 8 else (4 if ndev >= 4 else 2)
+    L, steps = 128, 9
+    s = sim.Settings(L=L, precision=prec, backend="B200", noise=noise, **PHYS)
+    ranks = []
+    for r in range(nranks):
+        mcd = sim.init_domain(s, r, nranks)
+        ranks.append((mcd, sim.init_fields(s, mcd, prec, seed=9, device=r % ndev)))
+    sim.connect_local([f for _, f in ranks])
+    sim.iterate_group([f for _, f in ranks], s, nsteps=steps)
+    o = orc.Oracle(L, prec, dims=orc.dims_create(nranks), noise=noise, seed=9, **PHYS)
+    o.step(steps)
+    for r, (mcd, f) in enumerate(ranks):
+        u, v = sim.get_fields(f)
+        uo, vo = o.get_fields(r)
+        assert np.array_equal(u, uo) and np.array_equal(v, vo), r
+        f.close()
