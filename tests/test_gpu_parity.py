@@ -597,3 +597,27 @@ def test_full_size_L1024_noise_statistics(sim, orc):
     # v is non-zero only around the initial block: its total mass does not depend on L
     assert abs(sv["sum"] - vo.sum()) < 0.03 * vo.sum()
     assert su["min"] > -0.5 and su["max"] < 2.0 and sv["min"] >= -1e-3
+
+
+def test_bench_own_arm_prints_one_json_line():
+    """bench.py on a small grid: one JSON line with every key of the contract."""
+    import json
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--L", "128", "--steps", "20", "--warmup", "3",
+                        "--e2e-steps", "2"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "clocks", "gpu_launches", "roofline", "e2e", "cpu_baseline"):
+        assert key in d, key
+    assert d["n_gpus"] == 1 and d["steps"] == 20 and d["gpu_launches"] == 20 and d["value"] > 1.0
+    for key in ("bound", "achieved", "peak", "unit", "frac", "traffic"):
+        assert key in d["roofline"], key
+    assert d["roofline"]["bound"] == "hbm" and abs(d["roofline"]["frac"] - d["roofline"]["achieved"] / d["roofline"]["peak"]) < 1e-9
+    assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["e2e"]["d2h_bytes_per_step"] > 0 and d["e2e"]["value"] > 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["value"] > 0
