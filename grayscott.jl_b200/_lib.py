@@ -71,6 +71,9 @@ _PROTOS = [
     ("gsb_timers_enable", _i, [_vp, _i]),
     ("gsb_timers", _i, [_vp, C.POINTER(C.c_double)]),
     ("gsb_halo_bytes", _i, [_vp, C.POINTER(_i64)]),
+    ("gsb_halo_timers", _i, [_vp, _i, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                             C.POINTER(_i64), C.POINTER(_i)]),
+    ("gsb_device_count", _i, [C.POINTER(_i)]),
     ("gsb_launch_count", _i, [_vp, C.POINTER(_i64)]),
     ("gsb_compute_stream", _i, [_vp, C.POINTER(_vp)]),
     ("gsb_calculate_arrays", _i, [_i, _i, C.POINTER(_i64), C.POINTER(_i64), _vp, _vp, _vp, _vp] +

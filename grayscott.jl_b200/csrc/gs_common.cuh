@@ -51,10 +51,12 @@ struct Params {
     int noise_fast;
     // native Float32 arithmetic
     float fDu, fDv, fF, fFK, fdt, fnoise;
+    float fnoise_s;      // noise * 2^-23: multiplies the integer-valued variate of noise_r32
     float fDu6, fDv6;    // Du/6, Dv/6
     int dt_is_one;       // dt == 1 exactly: x * dt == x, multiply skipped (bit-identical)
     // noise: Philox4x32-10 keyed on (seed, step, global cell)
     unsigned seed_lo, seed_hi, step;
+    unsigned pk[10][2];  // Philox round keys: seed + r * (0x9E3779B9, 0xBB67AE85)
     int gx0, gy0, gz0;   // global 0-based coordinate of local interior cell (0,0,0) = proc_offsets
 };
 

@@ -212,6 +212,8 @@ cudaError_t launch_unpack_faces(int dtype, void* u, void* v, const Layout& L, co
 // _compute_pdf (src/analysis/pdfcalc.jl:13-49, unfinished in the reference): for every z slice a
 // histogram of `nbins` equal bins over [min, max]; bin = floor((value - min) / bin_width) evaluated in
 // T, value == max falls into the last bin, values outside the range are not counted.
+// grid = (z slices, row groups): a CTA histograms its share of the slice's rows in shared memory and
+// adds the non-empty bins to the slice's histogram in global memory (zeroed by the launcher).
 template <typename T>
 __global__ void pdf_kernel(const T* __restrict__ f, Layout L, int nbins, T vmin, T vmax, T bin_width,
                            unsigned* __restrict__ pdf) {
@@ -219,28 +221,37 @@ __global__ void pdf_kernel(const T* __restrict__ f, Layout L, int nbins, T vmin,
     for (int b = threadIdx.x; b < nbins; b += blockDim.x) hist[b] = 0;
     __syncthreads();
     const int z = blockIdx.x;
-    const long long cells = (long long)L.sx * L.sy;
-    for (long long c = threadIdx.x; c < cells; c += blockDim.x) {
-        const int y = (int)(c / L.sx), x = (int)(c % L.sx);
-        const T v = f[L.idx(x, y, z)];
-        if (v < vmin || v > vmax) continue;
-        int bin = (int)floor((v - vmin) / bin_width);
-        if (bin >= nbins) bin = nbins - 1;
-        atomicAdd(&hist[bin], 1u);
+    for (int y = blockIdx.y; y < L.sy; y += gridDim.y) {
+        const T* row = f + L.idx(0, y, z);
+        for (int x = threadIdx.x; x < L.sx; x += blockDim.x) {
+            const T v = row[x];
+            if (!(v >= vmin && v <= vmax)) continue;       // outside the window, or NaN: not counted
+            int bin = (int)floor((v - vmin) / bin_width);
+            bin = bin < 0 ? 0 : (bin >= nbins ? nbins - 1 : bin);
+            atomicAdd(&hist[bin], 1u);
+        }
     }
     __syncthreads();
-    for (int b = threadIdx.x; b < nbins; b += blockDim.x) pdf[(long long)z * nbins + b] = hist[b];
+    for (int b = threadIdx.x; b < nbins; b += blockDim.x)
+        if (hist[b]) atomicAdd(&pdf[(long long)z * nbins + b], hist[b]);
 }
 
 cudaError_t launch_pdf(int dtype, const void* f, const Layout& L, int nbins, double vmin, double vmax,
                        unsigned* pdf_dev, cudaStream_t st) {
     const size_t smem = sizeof(unsigned) * (size_t)nbins;
+    cudaError_t e = cudaMemsetAsync(pdf_dev, 0, sizeof(unsigned) * (size_t)nbins * (size_t)L.sz, st);
+    if (e != cudaSuccess) return e;
+    // enough CTAs to fill the GPU (148 SMs x 8) without splitting small slices into crumbs
+    int groups = (148 * 8 + L.sz - 1) / L.sz;
+    if (groups > (L.sy + 7) / 8) groups = (L.sy + 7) / 8;
+    if (groups < 1) groups = 1;
+    dim3 grid((unsigned)L.sz, (unsigned)groups);
     if (dtype == DT_F32) {
         const float lo = (float)vmin, hi = (float)vmax, w = (hi - lo) / (float)nbins;
-        pdf_kernel<float><<<L.sz, 256, smem, st>>>((const float*)f, L, nbins, lo, hi, w, pdf_dev);
+        pdf_kernel<float><<<grid, 256, smem, st>>>((const float*)f, L, nbins, lo, hi, w, pdf_dev);
     } else {
         const double w = (vmax - vmin) / (double)nbins;
-        pdf_kernel<double><<<L.sz, 256, smem, st>>>((const double*)f, L, nbins, vmin, vmax, w, pdf_dev);
+        pdf_kernel<double><<<grid, 256, smem, st>>>((const double*)f, L, nbins, vmin, vmax, w, pdf_dev);
     }
     return cudaGetLastError();
 }

@@ -88,15 +88,9 @@ __global__ void plane_stats_final_kernel(const double* __restrict__ scratch, int
 std::mutex g_mu;
 double* g_scratch_ptr[64] = {};     // device address of g_noalloc_scratch, per device ordinal
 
-}  // namespace
-
-// errbuf (may be NULL) receives the reason when the call returns non-zero: this entry point keeps
-// no state of its own besides the scratch pointer, so it does not use gsb_last_error().
-extern "C" int gsb_field_stats_noalloc(int dtype, const int64_t sizes[3], const void* field_dev, double thresh,
-                                       double* out_dev, void* stream, char* errbuf, size_t errbuf_len) {
-    char dummy[1];
-    char* g_msg = errbuf && errbuf_len ? errbuf : dummy;
-    const size_t g_len = errbuf && errbuf_len ? errbuf_len : sizeof dummy;
+// the work; a non-zero result leaves the reason in g_msg
+int stats_noalloc(int dtype, const int64_t sizes[3], const void* field_dev, double thresh, double* out_dev,
+                  void* stream, char* g_msg, size_t g_len) {
     g_msg[0] = 0;
     if (!sizes || !field_dev || !out_dev) {
         snprintf(g_msg, g_len, "gsb_field_stats_noalloc: null argument");
@@ -152,4 +146,20 @@ extern "C" int gsb_field_stats_noalloc(int dtype, const int64_t sizes[3], const 
         return 1;
     }
     return 0;
+}
+
+}  // namespace
+
+namespace gsb { void set_last_error(const char* msg); }   // gsb200_api.cu: the message gsb_last_error() returns
+
+// On failure the reason goes to errbuf (when the caller passed one) and, like every other entry point
+// of this library, to gsb_last_error() of the calling thread.  On success the two kernels are only
+// enqueued: out_dev holds the results once `stream` has completed.
+extern "C" int gsb_field_stats_noalloc(int dtype, const int64_t sizes[3], const void* field_dev, double thresh,
+                                       double* out_dev, void* stream, char* errbuf, size_t errbuf_len) {
+    char msg[320];
+    const int rc = stats_noalloc(dtype, sizes, field_dev, thresh, out_dev, stream, msg, sizeof msg);
+    if (errbuf && errbuf_len) snprintf(errbuf, errbuf_len, "%s", msg);
+    if (rc != 0) gsb::set_last_error(msg);
+    return rc;
 }

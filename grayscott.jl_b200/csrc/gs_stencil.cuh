@@ -146,14 +146,20 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// The suspend-time hint lets the hardware park the warp instead of re-issuing the poll: without it a
+// waiting consumer warp spent 11-22 issue slots per plane on PHASECHK / BRA / YIELD (ncu source
+// page, round 1), slots the computing warps of the instruction-bound variants need.
+#ifndef GSB_MBAR_HINT_NS
+#define GSB_MBAR_HINT_NS 20000u
+#endif
 __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity), "r"(GSB_MBAR_HINT_NS) : "memory");
 }
 __device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, int c0, int c1, int c2,
                                             unsigned bar) {
@@ -358,7 +364,7 @@ naive_reflayout_kernel(const T* __restrict__ u, const T* __restrict__ v, T* __re
     unsigned word = 0;
     if (NOISE) {
         const unsigned gx = (unsigned)(p.gx0 + x);
-        Philox4 ph = philox4x32_10(gx >> 2, (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), p.step, p.seed_lo, p.seed_hi);
+        Philox4 ph = philox4x32_10(gx >> 2, (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), p.step, p);
         const unsigned sel = gx & 3u;
         word = sel == 0 ? ph.w[0] : sel == 1 ? ph.w[1] : sel == 2 ? ph.w[2] : ph.w[3];
     }

@@ -20,6 +20,9 @@ using namespace gsb;
 // ------------------------------------------------------------------ errors
 static thread_local std::string g_err;
 
+// gs_noalloc.cu reports through the same thread-local message
+namespace gsb { void set_last_error(const char* msg) { g_err = msg ? msg : ""; } }
+
 static int fail(const char* fmt, ...) {
     char buf[512];
     va_list ap;
@@ -142,6 +145,13 @@ struct gsb_handle {
     int timers_on;
     cudaEvent_t tev[6];     // comm begin/end, compute begin, interior end, compute end, (spare)
     bool timers_valid;
+    // per-piece halo timers: [piece][0..3] = before pack, after pack, after the transport, after unpack
+    cudaEvent_t pev[GSB_MAX_CHUNKS + 1][4];
+    long long piece_bytes[GSB_MAX_CHUNKS + 1];   // bytes this rank sent with the piece
+    int pieces_timed;       // pieces recorded by the last step (0: none)
+    int piece_cursor;       // slot the next enqueue_pack_send records into
+    unsigned* pdf_dev;      // gsb_pdf: device histogram, grown on demand
+    size_t pdf_cap;
     long long launches;     // kernels launched by this handle (bench.py's gpu_launches)
 };
 
@@ -176,8 +186,13 @@ static Params make_params(const gsb_handle* h) {
     p.noise_fast = p.noise == 0.0 || (std::isnormal(p.noise_s) && ldexp(p.noise_s, 31) == p.noise);
     p.fDu6 = p.fDu / 6.0f;
     p.fDv6 = p.fDv / 6.0f;
+    p.fnoise_s = ldexpf(p.fnoise, -23);
     p.seed_lo = (unsigned)(c.seed & 0xffffffffu);
     p.seed_hi = (unsigned)(c.seed >> 32);
+    for (unsigned r = 0; r < 10; ++r) {
+        p.pk[r][0] = p.seed_lo + r * 0x9E3779B9u;
+        p.pk[r][1] = p.seed_hi + r * 0xBB67AE85u;
+    }
     p.step = (unsigned)h->step;
     p.gx0 = (int)c.offsets[0]; p.gy0 = (int)c.offsets[1]; p.gz0 = (int)c.offsets[2];
     return p;
@@ -333,6 +348,9 @@ extern "C" int gsb_destroy(gsb_t* h) {
     if (h->ev_chunk) cudaEventDestroy(h->ev_chunk);
     for (int k = 0; k < GSB_MAX_CHUNKS; ++k) if (h->ev_piece[k]) cudaEventDestroy(h->ev_piece[k]);
     for (int i = 0; i < 6; ++i) if (h->tev[i]) cudaEventDestroy(h->tev[i]);
+    for (int k = 0; k <= GSB_MAX_CHUNKS; ++k)
+        for (int q = 0; q < 4; ++q) if (h->pev[k][q]) cudaEventDestroy(h->pev[k][q]);
+    if (h->pdf_dev) cudaFree(h->pdf_dev);
     delete h;
     return 0;
 }
@@ -389,6 +407,8 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
         h->fuse_x = fx ? atoi(fx) : 0;
     }
     for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&h->tev[i]));
+    for (int k = 0; k <= GSB_MAX_CHUNKS; ++k)
+        for (int q = 0; q < 4; ++q) CK(cudaEventCreate(&h->pev[k][q]));
     h->n_active = 0;
     for (int d = 0; d < 6; ++d) {
         h->active[d] = c.neighbors[d] >= 0;
@@ -572,7 +592,9 @@ extern "C" int gsb_get_step(gsb_t* h, int64_t* step) {
 }
 extern "C" int gsb_set_step(gsb_t* h, int64_t step) {
     if (!h) return fail("null handle");
+    if (step < 0) return fail("gsb_set_step: step < 0");
     h->step = step;
+    h->ghost_valid = false;   // receive buffers and message parity follow the step number: exchange again
     return 0;
 }
 
@@ -613,12 +635,15 @@ extern "C" int gsb_pdf(gsb_t* h, int which, int nbins, double vmin, double vmax,
     }
     DeviceGuard guard_(h->device);
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
-    unsigned* dev = nullptr;
     CK(cudaStreamSynchronize(h->s_comm));
-    CK(cudaMallocAsync((void**)&dev, n * sizeof(unsigned), h->s_compute));
+    if (h->pdf_cap < n) {                                   // histogram buffer kept by the handle, grown on demand
+        if (h->pdf_dev) { CK(cudaFree(h->pdf_dev)); h->pdf_dev = nullptr; h->pdf_cap = 0; }
+        CK(cudaMalloc((void**)&h->pdf_dev, n * sizeof(unsigned)));
+        h->pdf_cap = n;
+    }
+    unsigned* dev = h->pdf_dev;
     cudaError_t e = launch_pdf(h->cfg.dtype, h->f[which], h->L, nbins, vmin, vmax, dev, h->s_compute);
     if (e == cudaSuccess) e = cudaMemcpyAsync(pdf_host, dev, n * sizeof(unsigned), cudaMemcpyDeviceToHost, h->s_compute);
-    cudaFreeAsync(dev, h->s_compute);
     if (e != cudaSuccess) return fail("gsb_pdf: %s", cudaGetErrorString(e));
     CK(cudaStreamSynchronize(h->s_compute));
     return 0;
@@ -659,11 +684,39 @@ extern "C" int gsb_timers(gsb_t* h, double out_ms[4]) {
     if (!h->timers_on || !h->timers_valid) return fail("gsb_timers: enable timers and run gsb_step first");
     if (gsb_sync(h)) return 1;
     float a = 0, b = 0, c = 0, d = 0;
-    if (h->n_active) CK(cudaEventElapsedTime(&a, h->tev[0], h->tev[1]));
+    for (int k = 0; k < h->pieces_timed; ++k) {                 // pack -> transport -> unpack, every piece of the step
+        float t = 0;
+        CK(cudaEventElapsedTime(&t, h->pev[k][0], h->pev[k][3]));
+        a += t;
+    }
     CK(cudaEventElapsedTime(&b, h->tev[2], h->tev[3]));
     CK(cudaEventElapsedTime(&c, h->tev[5], h->tev[4]));   // shell kernels only, after the halo arrived
     CK(cudaEventElapsedTime(&d, h->tev[2], h->tev[4]));
     out_ms[0] = a; out_ms[1] = b; out_ms[2] = c; out_ms[3] = d;
+    return 0;
+}
+extern "C" int gsb_halo_timers(gsb_t* h, int max_pieces, double* pack_ms, double* wire_ms, double* unpack_ms,
+                               int64_t* bytes, int* npieces) {
+    if (!h || !npieces) return fail("null argument");
+    if (!h->timers_on) return fail("gsb_halo_timers: enable timers and run gsb_step first");
+    if (gsb_sync(h)) return 1;
+    const int n = h->pieces_timed < max_pieces ? h->pieces_timed : max_pieces;
+    for (int k = 0; k < n; ++k) {
+        float p = 0, w = 0, u = 0;
+        CK(cudaEventElapsedTime(&p, h->pev[k][0], h->pev[k][1]));
+        CK(cudaEventElapsedTime(&w, h->pev[k][1], h->pev[k][2]));
+        CK(cudaEventElapsedTime(&u, h->pev[k][2], h->pev[k][3]));
+        if (pack_ms) pack_ms[k] = p;
+        if (wire_ms) wire_ms[k] = w;
+        if (unpack_ms) unpack_ms[k] = u;
+        if (bytes) bytes[k] = h->piece_bytes[k];
+    }
+    *npieces = n;
+    return 0;
+}
+extern "C" int gsb_device_count(int* count) {
+    if (!count) return fail("null argument");
+    CK(cudaGetDeviceCount(count));
     return 0;
 }
 extern "C" int gsb_halo_bytes(gsb_t* h, int64_t* bytes) {
@@ -818,7 +871,13 @@ static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, c
     DeviceGuard guard_(h->device);
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamWaitEvent(h->s_comm, after, 0));               // the cells to send are final
-    if (h->timers_on) CK(cudaEventRecord(h->tev[0], h->s_comm));
+    const int slot = h->piece_cursor <= GSB_MAX_CHUNKS ? h->piece_cursor : GSB_MAX_CHUNKS;
+    if (h->timers_on) {
+        CK(cudaEventRecord(h->pev[slot][0], h->s_comm));
+        long long b = 0;
+        for (int d = 0; d < 6; ++d) if (pc.send[d]) b += 2 * face_piece_elems(h->L, d, pc.z0, pc.z1) * (long long)h->es;
+        h->piece_bytes[slot] = b;
+    }
     FaceSet fs;
     fs.n = 0;
     for (int d = 0; d < 6; ++d) {
@@ -834,6 +893,7 @@ static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, c
         CK(launch_pack_faces(h->cfg.dtype, h->f[2 * src], h->f[2 * src + 1], h->L, fs, h->s_comm));
         h->launches += 1;
     }
+    if (h->timers_on) CK(cudaEventRecord(h->pev[slot][1], h->s_comm));
     if (h->transport == TR_NCCL && !(debug_skip() & 2)) {
         const ncclDataType_t ty = h->cfg.dtype == GSB_F32 ? ncclFloat : ncclDouble;
         NK(g_nccl.GroupStart());
@@ -845,6 +905,7 @@ static int enqueue_pack_send(gsb_handle* h, const Piece& pc, int src, int par, c
         }
         NK(g_nccl.GroupEnd());
     }
+    if (h->timers_on) CK(cudaEventRecord(h->pev[slot][2], h->s_comm));
     CK(cudaEventRecord(h->ev_packed, h->s_comm));
     return 0;
 }
@@ -870,7 +931,12 @@ static int enqueue_unpack(gsb_handle* h, const Piece& pc, int dst, int par, cuda
         CK(launch_unpack_faces(h->cfg.dtype, h->f[2 * dst], h->f[2 * dst + 1], h->L, fs, h->s_comm));
         h->launches += 1;
     }
-    if (h->timers_on) CK(cudaEventRecord(h->tev[1], h->s_comm));
+    if (h->timers_on) {
+        const int slot = h->piece_cursor <= GSB_MAX_CHUNKS ? h->piece_cursor : GSB_MAX_CHUNKS;
+        CK(cudaEventRecord(h->pev[slot][3], h->s_comm));
+        if (h->piece_cursor < GSB_MAX_CHUNKS) h->piece_cursor += 1;
+        h->pieces_timed = h->piece_cursor;
+    }
     CK(cudaEventRecord(done, h->s_comm));
     return 0;
 }
@@ -1073,7 +1139,7 @@ static int pipeline_step(gsb_handle** hs, int n) {
     chunk_order(C, order);
     Params ps[64];
     if (n > 64) return fail("too many in-process ranks");
-    for (int r = 0; r < n; ++r) ps[r] = make_params(hs[r]);
+    for (int r = 0; r < n; ++r) { ps[r] = make_params(hs[r]); hs[r]->piece_cursor = 0; hs[r]->pieces_timed = 0; }
     for (int i = 0; i < C; ++i) {
         const int k = order[i];
         for (int r = 0; r < n; ++r) {
@@ -1093,6 +1159,7 @@ static int pipeline_step(gsb_handle** hs, int n) {
 }
 
 static int split_step(gsb_handle** hs, int n) {
+    for (int r = 0; r < n; ++r) { hs[r]->piece_cursor = 0; hs[r]->pieces_timed = 0; }
     for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_exchange_now(hs[r], false)) return 1;
     for (int r = 0; r < n; ++r) if (hs[r]->n_active) if (enqueue_exchange_now(hs[r], true)) return 1;
     for (int r = 0; r < n; ++r) if (enqueue_compute_overlapped(hs[r])) return 1;
@@ -1105,6 +1172,7 @@ extern "C" int gsb_exchange(gsb_t* h) {
     if (!h->n_active) return 0;
     if (check_transport(h)) return 1;
     if (h->transport == TR_LOCAL) return fail("gsb_exchange: in-process handles advance together, use gsb_step_group");
+    h->piece_cursor = 0; h->pieces_timed = 0;
     if (enqueue_exchange_now(h, false)) return 1;
     if (enqueue_exchange_now(h, true)) return 1;
     h->ghost_valid = false;   // whole-face message layout: a later gsb_step exchanges again in its own layout
@@ -1117,7 +1185,14 @@ extern "C" int gsb_calculate(gsb_t* h) {
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     if (ensure_maps(h)) return 1;
     const Params p = make_params(h);
-    if (h->n_active) CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+    if (h->n_active) {
+        // everything enqueued on the communication stream so far (gsb_exchange's unpack, or the pieces a
+        // pipelined gsb_step sent ahead) must have landed in the ghosts
+        CK(cudaEventRecord(h->ev_halo, h->s_comm));
+        CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
+        CK(cudaStreamWaitEvent(h->s_compute2, h->ev_halo, 0));
+    }
+    if (h->n_active && fused_x(h) == 2 && h->ghost_valid) if (refresh_x_ghosts(h)) return 1;
     if (launch_box(h, full_box(h), p)) return 1;
     CK(cudaEventRecord(h->ev_compute, h->s_compute));
     return 0;

@@ -12,8 +12,9 @@
  *    (the reference maps any failure to exit code 1, src/GrayScott.jl:40-48).
  *  - one handle = one subdomain = one GPU (the reference: one MPI rank, one Fields).  Handles
  *    are used from one host thread at a time.  Several handles per process are allowed.
- *  - step/exchange/calculate/swap only ENQUEUE work on the handle's CUDA streams; they do not
- *    synchronise with the host.  gsb_get_* / gsb_sync / gsb_field_stats / gsb_destroy do.
+ *  - step/exchange/calculate/swap (and gsb_calculate_arrays, gsb_field_stats_noalloc on the
+ *    caller's stream) only ENQUEUE work; they do not synchronise with the host.
+ *    gsb_get_* / gsb_sync / gsb_field_stats / gsb_pdf / gsb_timers / gsb_destroy do.
  *  - host arrays use the REFERENCE layout: x fastest, then y, then z
  *    (Julia Array{T,3}(nx, ny, nz), column-major).  Device memory is owned by the library in
  *    its own padded layout and is never exposed.
@@ -161,6 +162,9 @@ int gsb_alloc_host(void** out, size_t bytes);
 int gsb_free_host(void* p);
 
 int gsb_sync(gsb_t* h);
+/* The step counter (= number of swaps since gsb_init_fields): the noise counter, and the parity that
+ * selects receive buffers.  Set it together with gsb_set_ghosted to resume a run (restart,
+ * Structs.jl:15-19): the next step then exchanges the ghosts afresh. */
 int gsb_get_step(gsb_t* h, int64_t* step);
 int gsb_set_step(gsb_t* h, int64_t step);
 
@@ -197,11 +201,25 @@ int gsb_set_kernel(gsb_t* h, int kind, int ty, int stages, int zchunk);
 int gsb_get_kernel(gsb_t* h, int* kind, int* ty, int* stages, int* zchunk);
 
 /* Per-phase device times of the LAST step enqueued by gsb_step (ms): out[0] = halo (pack,
- * transport, unpack), out[1] = interior update, out[2] = shell update (after the halo
- * arrived), out[3] = whole step.
+ * transport, unpack; summed over the pieces of the step, see gsb_halo_timers), out[1] = interior
+ * update, out[2] = shell update after the halo arrived (split scheme only; the pipelined scheme
+ * has no shell kernels), out[3] = whole step.
  * Enable before stepping; synchronises when read. */
 int gsb_timers_enable(gsb_t* h, int on);
 int gsb_timers(gsb_t* h, double out_ms[4]);
+
+/* The halo exchange of the LAST step piece by piece (the reference: the 12 MPI.Sendrecv! of
+ * communication.jl:146-177; here one piece per z chunk of the pipelined scheme, or one piece for the
+ * whole faces): device time of the pack kernel, of the transport (NCCL send/recv group, which
+ * includes waiting for the neighbour to reach the same point; 0 for in-process ranks, whose pack
+ * kernel writes into the neighbour's buffer directly) and of the unpack kernel, plus the bytes this
+ * rank sent with the piece.  Arrays of max_pieces entries (any may be NULL); *npieces = entries
+ * filled.  Enable the timers before stepping; synchronises when read. */
+int gsb_halo_timers(gsb_t* h, int max_pieces, double* pack_ms, double* wire_ms, double* unpack_ms,
+                    int64_t* bytes, int* npieces);
+
+/* cudaGetDeviceCount, for hosts that map node-local ranks to devices without a CUDA binding. */
+int gsb_device_count(int* count);
 
 /* Halo bytes this handle sends per step (u and v faces to all real neighbours). */
 int gsb_halo_bytes(gsb_t* h, int64_t* bytes);
@@ -240,7 +258,9 @@ int gsb_calculate_arrays(int dtype, int arith, const int64_t sizes[3], const int
  *   field_dev : DEVICE array in the reference layout, ghosted: (sx+2)(sy+2)(sz+2), x fastest
  *   out_dev   : 5 doubles the GPU can write (device or pinned host memory), caller-owned
  *   stream    : a cudaStream_t or NULL; the call only enqueues two kernels
- *   errbuf    : optional; receives the reason when the result is non-zero
+ *   errbuf    : optional; receives the reason when the result is non-zero (gsb_last_error()
+ *               returns the same message)
+ * Like step/exchange/calculate it only enqueues: out_dev is valid once `stream` has completed.
  *
  * The per-plane partial results go to a fixed array inside the library image (160 KiB of device
  * memory on every GPU that loads the library, held until exit), so:

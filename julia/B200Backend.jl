@@ -6,11 +6,23 @@
 # (src/simulation/Inputs.jl:110-120) and reaches these methods through the Val dispatch of
 # src/simulation/public.jl:18-25,45-53.
 #
-# NOT EXECUTED in this repository's CI: the build machines have no Julia (SURVEY.md K13).  The same
-# C ABI is exercised by the Python mirror grayscott.jl_b200/simulation.py, test for test.
+# NOT EXECUTED in this repository's CI: the build machines have no Julia (SURVEY.md K13).  What is
+# checked instead: tests/test_glue_layout.py parses `struct GsbConfig` below and compares it field by
+# field (order, width, offset) with the C struct, builds a ctypes structure FROM this file's definition
+# and replays this file's ccall sequence with it on a GPU; the Python mirror
+# grayscott.jl_b200/simulation.py exercises the same C ABI test for test.
 #
 #   julia --project -e 'include("julia/B200Backend.jl"); GrayScott.main(["cfg.toml"])'
 #
+# Environment (all optional):
+#   GSB200_LIB    path of libgsb200.so (default: ../grayscott.jl_b200/libgsb200.so)
+#   GSB_ARITH     "reference" (default): Float32 runs use the reference's mixed Float32/Float64
+#                 promotion, bit-identical to the CPU backend at noise = 0, at ~85 % of the speed;
+#                 "native": Float32 FMAs, within 1e-5 of the CPU backend (the benchmark headline)
+#   GSB_SEED      noise key, decimal or 0x-hex (default 0x5EED: every run repeats the same noise;
+#                 "random" draws one from the clock on rank 0 and broadcasts it, like the reference's
+#                 unseeded RNG)
+#   GSB_DEVICE    CUDA device ordinal of this rank (default: node-local rank modulo the device count)
 module B200Backend
 
 import MPI
@@ -56,11 +68,12 @@ mutable struct Handle
 end
 
 """
-Opaque device array of one `Fields` slot.  The library owns the memory (padded layout); the
-wrapper only remembers which slot it names NOW: `iterate!` swaps the wrappers' slots like
-public.jl:67-68 swaps the references.  `Array(a)` is the ghosted device-to-host copy.
+Opaque device array of one `Fields` slot.  The library owns the memory (padded layout) and the
+ping-pong binding: slot GSB_U always names the CURRENT u, GSB_U_TEMP the array the next calculate!
+writes.  `iterate!` and `swap!` re-bind inside the library (gsb_step / gsb_swap); the wrappers are
+never exchanged on the Julia side.  `Array(a)` is the ghosted device-to-host copy.
 """
-mutable struct B200Array{T, N} <: AbstractArray{T, N}
+struct B200Array{T, N} <: AbstractArray{T, N}
     handle::Handle
     slot::Cint                      # GSB_U, GSB_V, GSB_U_TEMP, GSB_V_TEMP
     dims::NTuple{N, Int}
@@ -78,16 +91,32 @@ gsb_dtype(::Type{Float64}) = Int32(1)
 
 const NEIGHBORS = ("west", "east", "down", "up", "south", "north")   # communication.jl:90-92
 
+gsb_arith() = lowercase(get(ENV, "GSB_ARITH", "reference")) in ("native", "1") ? Int32(1) : Int32(0)
+
+function gsb_seed(comm)
+    s = get(ENV, "GSB_SEED", "0x5EED")
+    seed = Ref{UInt64}(lowercase(s) == "random" ? UInt64(time_ns()) : parse(UInt64, s))
+    MPI.Bcast!(seed, 0, comm)           # one key for the whole run: the noise must not depend on the rank
+    return seed[]
+end
+
+function gsb_device(comm)
+    haskey(ENV, "GSB_DEVICE") && return parse(Int32, ENV["GSB_DEVICE"])
+    node = MPI.Comm_split_type(comm, MPI.COMM_TYPE_SHARED, MPI.Comm_rank(comm))
+    n = Ref{Cint}(0)
+    check(ccall((:gsb_device_count, libgsb), Cint, (Ptr{Cint},), n))
+    return Int32(MPI.Comm_rank(node) % max(n[], 1))
+end
+
 function Simulation.init_fields(::Val{:b200}, ::Val{:plain}, settings::Settings, mcd::MPICartDomain, T)
     rank = MPI.Comm_rank(mcd.cart_comm)
     nranks = MPI.Comm_size(mcd.cart_comm)
-    ngpu = Ref{Cint}(1)   # one rank per GPU of the node, like ext/CUDAExt.jl's device selection
-    cfg = GsbConfig(gsb_dtype(T), Int32(get(ENV, "GSB_ARITH", "0") == "1" ? 1 : 0), settings.L, (0, 0, 0),
+    cfg = GsbConfig(gsb_dtype(T), gsb_arith(), settings.L, (0, 0, 0),
                     Tuple(Int32.(mcd.dims)), Tuple(Int32.(mcd.coords)), Tuple(mcd.proc_sizes),
                     Tuple(mcd.proc_offsets),
                     Tuple(Int32(n == MPI.PROC_NULL ? -1 : n) for n in (mcd.proc_neighbors[k] for k in NEIGHBORS)),
                     settings.Du, settings.Dv, settings.F, settings.k, settings.dt, settings.noise,
-                    UInt64(0x5EED), Int32(rank % parse(Int, get(ENV, "GSB_GPUS_PER_NODE", "8"))), Int32(rank), Int32(nranks))
+                    gsb_seed(mcd.cart_comm), gsb_device(mcd.cart_comm), Int32(rank), Int32(nranks))
     out = Ref{Ptr{Cvoid}}(C_NULL)
     check(ccall((:gsb_create, libgsb), Cint, (Ptr{Ptr{Cvoid}}, Ref{GsbConfig}), out, cfg))
     h = Handle(out[])
@@ -105,31 +134,73 @@ function Simulation.init_fields(::Val{:b200}, ::Val{:plain}, settings::Settings,
     return Fields(arr(0), arr(1), arr(2), arr(3), xy, xz, yz)
 end
 
+handle(fields::Fields) = fields.u.handle.ptr
+
+# The reference swaps `fields.u, fields.u_temp` by hand (public.jl:67-68).  Here the binding lives in the
+# library, so the wrappers must keep their roles; a caller that exchanged them would make every later
+# call address the wrong arrays.  Refuse loudly instead.
+function check_roles(fields::Fields)
+    (fields.u.slot == 0 && fields.v.slot == 1 && fields.u_temp.slot == 2 && fields.v_temp.slot == 3) ||
+        error("B200 backend: fields.u / fields.u_temp were exchanged on the Julia side; use B200Backend.swap!(fields) " *
+              "(or iterate!), which re-binds inside the library")
+    return nothing
+end
+
 # more specific than public.jl:54: skips the generic exchange! that stages GPU arrays through host
-# copies and drops the result (communication.jl:180-198)
+# copies and drops the result (communication.jl:180-198).  gsb_step = exchange -> calculate -> swap,
+# the swap being the library's own re-binding: the wrappers stay as they are.
 function Simulation.iterate!(::Val{:b200}, ::Val{:plain}, fields::Fields{T, 3, <:B200Array}, settings::Settings,
                              mcd::MPICartDomain) where {T}
-    check(ccall((:gsb_step, libgsb), Cint, (Ptr{Cvoid}, Cint), fields.u.handle.ptr, 1))
-    # the library swapped its bindings; the wrappers keep naming u/v/u_temp/v_temp, so nothing to swap here
+    check_roles(fields)
+    check(ccall((:gsb_step, libgsb), Cint, (Ptr{Cvoid}, Cint), handle(fields), 1))
     return
 end
 
+# The three pieces for callers that drive them separately: exchange!, calculate!, swap!.
 function Simulation.exchange!(fields::Fields{T, 3, <:B200Array}, mcd) where {T}
-    check(ccall((:gsb_exchange, libgsb), Cint, (Ptr{Cvoid},), fields.u.handle.ptr))
+    check_roles(fields)
+    check(ccall((:gsb_exchange, libgsb), Cint, (Ptr{Cvoid},), handle(fields)))
 end
 
 function Simulation.calculate!(::Val{:b200}, ::Val{:plain}, fields::Fields{T, 3, <:B200Array}, settings::Settings,
                                mcd::MPICartDomain) where {T}
-    check(ccall((:gsb_calculate, libgsb), Cint, (Ptr{Cvoid},), fields.u.handle.ptr))
+    check_roles(fields)
+    check(ccall((:gsb_calculate, libgsb), Cint, (Ptr{Cvoid},), handle(fields)))
 end
 
-# called by IO.write_step! (src/simulation/IO.jl:84-85)
+"""
+    swap!(fields)
+
+The `fields.u, fields.u_temp = fields.u_temp, fields.u` of public.jl:67-68 for this backend: gsb_swap
+re-binds u <-> u_temp and v <-> v_temp inside the library and advances the step (= noise) counter.
+After it `fields.u` names the new values again.  Do not exchange the wrappers by hand.
+"""
+function swap!(fields::Fields{T, 3, <:B200Array}) where {T}
+    check_roles(fields)
+    check(ccall((:gsb_swap, libgsb), Cint, (Ptr{Cvoid},), handle(fields)))
+end
+
+# called by IO.write_step! (src/simulation/IO.jl:84-85): blocking, returns fresh host arrays
 function Simulation.get_fields(::Val{:b200}, fields::Fields{T, 3, <:B200Array}) where {T}
+    check_roles(fields)
     sx, sy, sz = fields.u.dims .- 2
     u = Array{T, 3}(undef, sx, sy, sz)
     v = Array{T, 3}(undef, sx, sy, sz)
-    check(ccall((:gsb_get_fields, libgsb), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}), fields.u.handle.ptr, u, v))
+    check(ccall((:gsb_get_fields, libgsb), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}), handle(fields), u, v))
     return u, v
 end
+
+"""
+    get_fields_async!(fields, u, v); ...; output_wait(fields)
+
+Opt-in output path for a driver that can keep stepping while the copy drains: `u`, `v` are
+caller-owned host arrays of size (sx, sy, sz) that must stay alive (and should be pinned) until
+`output_wait` returns.  IO.write_step! as written needs the arrays at once, so it uses get_fields.
+"""
+function get_fields_async!(fields::Fields{T, 3, <:B200Array}, u::Array{T, 3}, v::Array{T, 3}) where {T}
+    check_roles(fields)
+    check(ccall((:gsb_get_fields_async, libgsb), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}), handle(fields), u, v))
+end
+output_wait(fields::Fields) = check(ccall((:gsb_output_wait, libgsb), Cint, (Ptr{Cvoid},), handle(fields)))
 
 end # module

@@ -13,7 +13,7 @@ int main(void) {
         (void*)gsb_get_unique_id, (void*)gsb_comm_init, (void*)gsb_comm_init_local, (void*)gsb_set_kernel,
         (void*)gsb_get_kernel, (void*)gsb_timers_enable, (void*)gsb_timers, (void*)gsb_halo_bytes,
         (void*)gsb_launch_count, (void*)gsb_compute_stream, (void*)gsb_calculate_arrays,
-        (void*)gsb_field_stats_noalloc,
+        (void*)gsb_field_stats_noalloc, (void*)gsb_halo_timers, (void*)gsb_device_count,
     };
     gsb_config cfg;
     int32_t dims[3];

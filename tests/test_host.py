@@ -38,7 +38,7 @@ def test_header_is_valid_c_and_links(pkg, tmp_path):
     assert r.returncode == 0, r.stderr
     r = subprocess.run([str(exe)], capture_output=True, text=True)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
-    assert "36 symbols, version 100" in r.stdout
+    assert "38 symbols, version 100" in r.stdout
     # the Python mirror of struct gsb_config has the same size as the C one
     assert f"sizeof(gsb_config) = {C.sizeof(pkg._lib.GsbConfig)}" in r.stdout
 
@@ -118,6 +118,11 @@ def test_no_gpu_fails_loudly(sim):
         sim.init_fields(s, sim.init_domain(s, 0, 1), "Float32")
 
 
+def argparse_namespace(gpus):
+    import argparse
+    return argparse.Namespace(gpus=gpus, L=64, global_L=0, scaling="weak", precision="Float32", noise=0.1, arith="native")
+
+
 _WORKER = r"""
 import os, sys
 sys.path.insert(0, {root!r})
@@ -166,16 +171,43 @@ def test_gloo_world_size_2(tmp_path):
         assert "ok" in out
 
 
-def test_bench_reference_arm_prints_one_json_line():
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 6, 8, 12, 16, 27, 30])
+def test_bench_dims_create_matches_library_and_oracle(sim, orc, n):
+    """bench.py computes the decomposition itself so that neither arm needs the other's library."""
+    import bench
+    assert bench.dims_create(n) == sim.dims_create(n) == orc.dims_create(n)
+
+
+_REF_ARM = r"""
+import os, runpy, sys
+sys.argv = ["bench.py", "--impl", "reference", "--steps", "2", "--warmup", "1", "--L", "64", "--gpus", "{gpus}"]
+runpy.run_path({bench!r}, run_name="__main__")
+maps = open("/proc/self/maps").read()
+assert "libgs_oracle" in maps, "the CPU arm must have run the oracle"
+assert "libgsb200" not in maps, "the CPU arm loaded the product library"
+assert "grayscott_jl_b200" not in sys.modules, "the CPU arm imported the product package"
+"""
+
+
+@pytest.mark.parametrize("gpus,launcher_env", [(1, {}), (4, {"OMP_NUM_THREADS": "1", "RANK": "0", "WORLD_SIZE": "4"})])
+def test_bench_reference_arm_prints_one_json_line(tmp_path, gpus, launcher_env):
     """bench.py --impl reference (the CPU arm the driver runs beside ours): exactly one JSON line on
-    stdout with the contract's keys."""
+    stdout with the contract's keys; the process never loads the product library; under
+    torch.distributed.run's OMP_NUM_THREADS=1 it still uses every core and the same sample."""
     import json
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2",
-                        "--warmup", "1", "--L", "64"], capture_output=True, text=True, timeout=300)
+    script = tmp_path / "ref_arm.py"
+    script.write_text(_REF_ARM.format(gpus=gpus, bench=os.path.join(ROOT, "bench.py")))
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, **launcher_env))
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
     assert len(lines) == 1, r.stdout
     d = json.loads(lines[0])
+    assert d["n_gpus"] == gpus and d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert "L=64 cube" in d["cpu_baseline"]["sample"] and "cpu_sample_L" not in d["config"]
+    import bench
+    a = argparse_namespace(gpus)
+    assert d["config"] == bench.workload_config(a, gpus)           # the own arm prints exactly this config
     for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
                 "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
         assert key in d, key
