@@ -32,10 +32,18 @@ __device__ __forceinline__ double div6_rn(double x) {
 
 // noise * r with r = ri * 2^-31, ri the integer-valued variate of gs_philox.cuh.  Scaling by a
 // power of two is exact, so RN(noise * r) == RN((noise * 2^-31) * ri) unless noise * 2^-31 leaves
-// the normal range; the host decides (Params::noise_fast) and both paths give the same bits.
+// the normal range; the host decides (Params::ref_mode) and both forms give the same bits.
+template <bool FAST>
 __device__ __forceinline__ double noise_term(const Params& p, double ri) {
-    return p.noise_fast ? __dmul_rn(p.noise_s, ri) : __dmul_rn(p.noise, __dmul_rn(ri, 0x1.0p-31));
+    return FAST ? __dmul_rn(p.noise_s, ri) : __dmul_rn(p.noise, __dmul_rn(ri, 0x1.0p-31));
 }
+
+// Variants of the reference arithmetic, chosen ONCE per vector by a warp-uniform branch on
+// Params::ref_mode.  (Left as per-operation conditions, nvcc turns `if (!dt_is_one) x *= dt` and the
+// noise form into compute-both-and-select: 4 DMUL + 5 FSEL per cell on the FP64-bound path, ncu r2.)
+enum : int { REF_DT1 = 0,      // dt == 1 exactly (x * 1 == x: multiply skipped) and noise * 2^-31 normal
+             REF_DT = 1,       // any dt, noise * 2^-31 normal
+             REF_GENERIC = 2 };// any dt, noise so small that noise * 2^-31 would be subnormal
 
 // Same quotient when x is an exact difference of Float32-derived values (the Float32 fields): such an
 // x is either zero or at least 2^-149 in magnitude, so no intermediate can underflow and only the sign
@@ -47,14 +55,16 @@ __device__ __forceinline__ double div6_rn_f32src(double x) {
     const double res = __fma_rn(r, c, q);
     // x = +-0 gives res = +0; the quotient of any other x already carries x's sign.  Copying the sign
     // bit of x is one LOP3 on the high word instead of a compare and two selects.
-    return __hiloint2double((__double2hiint(res) & 0x7fffffff) | (__double2hiint(x) & 0x80000000), __double2loint(res));
+    int hi;
+    asm("lop3.b32 %0, %1, %2, 0x80000000, 0xD8;" : "=r"(hi) : "r"(__double2hiint(res)), "r"(__double2hiint(x)));  // c ? b : a
+    return __hiloint2double(hi, __double2loint(res));
 }
 
 // su, sv: the left-folded six-neighbour sums ((((W+E)+S)+N)+D)+U computed in T by the caller.
 // r: integer-valued noise variate ri in [-2^31, 2^31) (reference) / r32 in [-1,1) (native); ignored
 // unless NOISE.
 
-template <bool NOISE>
+template <bool NOISE, int MODE>
 __device__ __forceinline__ void cell_update_ref(float uc, float vc, float su, float sv, double r,
                                                 const Params& p, float& un, float& vn) {
     const double u64 = (double)uc, v64 = (double)vc;
@@ -65,15 +75,15 @@ __device__ __forceinline__ void cell_update_ref(float uc, float vc, float su, fl
     const float fkv = __fmul_rn(p.fFK, vc);                        // (F + K) * v   (Float32)
     double du = __dsub_rn(__dmul_rn(p.Du, lap_u), (double)uvv);
     du = __dadd_rn(du, __dmul_rn(p.F, __dsub_rn(1.0, u64)));
-    if (NOISE) du = __dadd_rn(du, noise_term(p, r));
+    if (NOISE) du = __dadd_rn(du, noise_term<MODE != REF_GENERIC>(p, r));
     double dv = __dadd_rn(__dmul_rn(p.Dv, lap_v), (double)uvv);
     dv = __dsub_rn(dv, (double)fkv);
-    if (!p.dt_is_one) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
+    if (MODE != REF_DT1) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
     un = (float)__dadd_rn(u64, du);                                // one rounding on store
     vn = (float)__dadd_rn(v64, dv);
 }
 
-template <bool NOISE>
+template <bool NOISE, int MODE>
 __device__ __forceinline__ void cell_update_ref(double uc, double vc, double su, double sv, double r,
                                                 const Params& p, double& un, double& vn) {
     const double lap_u = div6_rn(__dsub_rn(su, __dmul_rn(6.0, uc)));
@@ -82,10 +92,10 @@ __device__ __forceinline__ void cell_update_ref(double uc, double vc, double su,
     const double fkv = __dmul_rn(p.FK, vc);
     double du = __dsub_rn(__dmul_rn(p.Du, lap_u), uvv);
     du = __dadd_rn(du, __dmul_rn(p.F, __dsub_rn(1.0, uc)));
-    if (NOISE) du = __dadd_rn(du, noise_term(p, r));
+    if (NOISE) du = __dadd_rn(du, noise_term<MODE != REF_GENERIC>(p, r));
     double dv = __dadd_rn(__dmul_rn(p.Dv, lap_v), uvv);
     dv = __dsub_rn(dv, fkv);
-    if (!p.dt_is_one) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
+    if (MODE != REF_DT1) { du = __dmul_rn(du, p.dt); dv = __dmul_rn(dv, p.dt); }
     un = __dadd_rn(uc, du);
     vn = __dadd_rn(vc, dv);
 }

@@ -49,6 +49,7 @@ struct Params {
     double FK;           // (F + K) added in T, then widened   (Simulation_CPU.jl:105)
     double noise_s;      // noise * 2^-31 (exactly), valid when noise_fast
     int noise_fast;
+    int ref_mode;        // REF_DT1 / REF_DT / REF_GENERIC (gs_arith.cuh): which variant of the reference arithmetic
     // native Float32 arithmetic
     float fDu, fDv, fF, fFK, fdt, fnoise;
     float fnoise_s;      // noise * 2^-23: multiplies the integer-valued variate of noise_r32
@@ -65,15 +66,16 @@ struct Box {
     int x0, x1, y0, y1, z0, z1;
 };
 
-// X faces carried by the update kernel itself (pipelined halo scheme, sx a multiple of the tile
-// width): instead of a separate strided gather/scatter over 2 * sy * sz cells, the lane that owns
-// column x = 0 (x = sx-1) stores its new values into the dense message buffer and reads its W (E)
-// ghost from the dense receive buffer.  Layout of a piece [zbase, zbase+nz): [u | v], element
-// y + sy * (z - zbase); the v part starts sy * nz elements later.  Null pointers switch a role off.
+// X faces carried by the update kernel itself (pipelined halo scheme, sx a multiple of the tile width,
+// sy a multiple of a 16-byte vector): instead of a separate strided gather/scatter over 2 * sy * sz cells,
+// the CTAs of the first / last x tile read their W / E ghosts from the dense receive buffer and write
+// their new boundary columns into the dense message buffer (bulk copies issued by the producer warp).
+// Layout of a piece [zbase, zbase+nz): [u | v], element y + sy * (z - zbase); the v part starts sy * nz
+// elements later.  A side is on when both of its pointers are set.
 struct XFaceArgs {
-    const void* ghost_lo;   // W ghosts for column x = 0        (null: read the ghost column of the array)
+    const void* ghost_lo;   // W ghosts for column x = 0        (null: side off, the array's ghost column is read)
     const void* ghost_hi;   // E ghosts for column x = sx-1
-    void* send_lo;          // new values of column x = 0       (null: not sent by the kernel)
+    void* send_lo;          // new values of column x = 0
     void* send_hi;          // new values of column x = sx-1
     int zbase, nz;
 };

@@ -24,15 +24,13 @@ namespace gsb {
 
 // Update the N cells of one vector.  *m/*0/*p: centre vectors at z-1/z/z+1; *s/*n: rows y-1/y+1
 // at z; *w/*e: the scalars left of a[0] and right of a[N-1] at z.
-template <typename T, int ARITH, bool NOISE>
-__device__ __forceinline__ void update_vec(const Vec<T>& um, const Vec<T>& u0, const Vec<T>& up,
-                                           const Vec<T>& us, const Vec<T>& un, T uw, T ue,
-                                           const Vec<T>& vm, const Vec<T>& v0, const Vec<T>& vp,
-                                           const Vec<T>& vs, const Vec<T>& vn, T vw, T ve,
-                                           const Params& p, int x, int y, int z, Vec<T>& uo, Vec<T>& vo) {
+template <typename T, int ARITH, bool NOISE, int MODE>
+__device__ __forceinline__ void update_cells(const Vec<T>& um, const Vec<T>& u0, const Vec<T>& up,
+                                             const Vec<T>& us, const Vec<T>& un, T uw, T ue,
+                                             const Vec<T>& vm, const Vec<T>& v0, const Vec<T>& vp,
+                                             const Vec<T>& vs, const Vec<T>& vn, T vw, T ve,
+                                             const Params& p, const unsigned (&words)[Vec<T>::N], Vec<T>& uo, Vec<T>& vo) {
     constexpr int N = Vec<T>::N;
-    unsigned words[N];
-    if (NOISE) noise_words<N>(p, (unsigned)(p.gx0 + x), (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), words);
 #pragma unroll
     for (int i = 0; i < N; ++i) {
         const T uW = i == 0 ? uw : u0.a[i == 0 ? 0 : i - 1];
@@ -48,8 +46,32 @@ __device__ __forceinline__ void update_vec(const Vec<T>& um, const Vec<T>& u0, c
         } else {
             double r = 0.0;
             if (NOISE) r = noise_r64(words[i]);
-            cell_update_ref<NOISE>(u0.a[i], v0.a[i], su, sv, r, p, uo.a[i], vo.a[i]);
+            cell_update_ref<NOISE, MODE>(u0.a[i], v0.a[i], su, sv, r, p, uo.a[i], vo.a[i]);
         }
+    }
+}
+
+template <typename T, int ARITH, bool NOISE>
+__device__ __forceinline__ void update_vec(const Vec<T>& um, const Vec<T>& u0, const Vec<T>& up,
+                                           const Vec<T>& us, const Vec<T>& un, T uw, T ue,
+                                           const Vec<T>& vm, const Vec<T>& v0, const Vec<T>& vp,
+                                           const Vec<T>& vs, const Vec<T>& vn, T vw, T ve,
+                                           const Params& p, int x, int y, int z, Vec<T>& uo, Vec<T>& vo) {
+    constexpr int N = Vec<T>::N;
+    unsigned words[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) words[i] = 0u;
+    if (NOISE) noise_words<N>(p, (unsigned)(p.gx0 + x), (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), words);
+    if constexpr (ARITH == ARITH_NATIVE) {
+        update_cells<T, ARITH, NOISE, REF_DT1>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, words, uo, vo);
+    } else {
+        // warp-uniform: one variant of the reference arithmetic for the whole vector
+        if (p.ref_mode == REF_DT1)
+            update_cells<T, ARITH, NOISE, REF_DT1>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, words, uo, vo);
+        else if (p.ref_mode == REF_DT)
+            update_cells<T, ARITH, NOISE, REF_DT>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, words, uo, vo);
+        else
+            update_cells<T, ARITH, NOISE, REF_GENERIC>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, words, uo, vo);
     }
 }
 
@@ -169,43 +191,61 @@ __device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map
         : "memory");
 }
 
+// 1-D bulk copies (the x-face columns of the fused halo scheme): global -> shared completing on an
+// mbarrier like the tensor loads, shared -> global in a bulk async-group.  16-byte aligned, n * 16 bytes.
+__device__ __forceinline__ void bulk_load_1d(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_store_1d(void* dst, unsigned src, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+
 template <typename T, int TY>
 struct TmaTile {
     static constexpr int N = Vec<T>::N;
     static constexpr int BW = 32 * N + 2 * N;                       // box width in elements (544 B)
     static constexpr int ROWS = TY + 2;
     static constexpr int BOX_BYTES = BW * ROWS * (int)sizeof(T);
-    static constexpr int FIELD_BYTES = (BOX_BYTES + 127) / 128 * 128;  // TMA dst alignment
-    static constexpr int STAGE_BYTES = 2 * FIELD_BYTES;
-    static constexpr size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 128 + 16 * stages; }
+    static constexpr int BOXR_BYTES = (BOX_BYTES + 127) / 128 * 128;   // TMA dst alignment
+    static constexpr int BOXR = BOXR_BYTES / (int)sizeof(T);           // first element after the box
+    // x-face side area behind each field's box (fused halo scheme only), TY elements each:
+    //   [W ghosts in | E ghosts in | column x = 0 out | column x = sx-1 out]
+    static constexpr int SIDE_BYTES = (4 * TY * (int)sizeof(T) + 127) / 128 * 128;
+    __host__ __device__ static constexpr int field_bytes(bool xf) { return BOXR_BYTES + (xf ? SIDE_BYTES : 0); }
+    __host__ __device__ static constexpr int stage_bytes(bool xf) { return 2 * field_bytes(xf); }
+    __host__ __device__ static constexpr size_t smem_bytes(int stages, bool xf) { return (size_t)stages * stage_bytes(xf) + 128 + 16 * stages; }
 };
 
 // One consumer iteration: plane index i of the chunk has landed in slot `cur`; am/a0 (bm/b0) hold
 // the centre vectors of planes i-2 / i-1, ap (bp) receives plane i; plane i-1 sits in slot `prev`.
 // The caller rotates the register names (three-way unrolled loop), so no register moves.
-template <typename T, int ARITH, bool NOISE, int TY, int XF>
-__device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsigned char* prev, int i,
+// XF: an edge lane that owns a subdomain boundary column (own_x) finds its x ghost at `eoff` in the side
+// area of the slot (put there by the producer) and leaves its new boundary value at eoff + 2 * TY.
+template <typename T, int ARITH, bool NOISE, int TY, bool XF>
+__device__ __forceinline__ void tma_consume(const unsigned char* cur, unsigned char* prev, int i,
                                             const Vec<T>& am, const Vec<T>& a0, Vec<T>& ap, const Vec<T>& bm,
                                             const Vec<T>& b0, Vec<T>& bp, const int roff, const int eoff,
                                             const bool lane_w, const bool lane_e, const bool vec_active,
                                             const Params& p, const Box& box, const int x, const int y, const int z,
-                                            T*& pou, T*& pov, const long long pxy, const bool own_x, const T gu,
-                                            const T gv, T* sp, const int svoff) {
+                                            T*& pou, T*& pov, const long long pxy, const bool own_x) {
     using Tile = TmaTile<T, TY>;
     constexpr int N = Tile::N;
+    constexpr int FB = Tile::field_bytes(XF);
     const T* su_ = reinterpret_cast<const T*>(cur);
-    const T* sv_ = reinterpret_cast<const T*>(cur + Tile::FIELD_BYTES);
+    const T* sv_ = reinterpret_cast<const T*>(cur + FB);
     ap = ld_vec(su_ + roff);
     bp = ld_vec(sv_ + roff);
     if (i >= 2) {
-        const T* pu_ = reinterpret_cast<const T*>(prev);
-        const T* pv_ = reinterpret_cast<const T*>(prev + Tile::FIELD_BYTES);
+        T* pu_ = reinterpret_cast<T*>(prev);
+        T* pv_ = reinterpret_cast<T*>(prev + FB);
         const Vec<T> us = ld_vec(pu_ + roff - Tile::BW), un = ld_vec(pu_ + roff + Tile::BW);
         const Vec<T> vs = ld_vec(pv_ + roff - Tile::BW), vn = ld_vec(pv_ + roff + Tile::BW);
-        // x neighbours across vectors: shuffles inside the warp, the box halo for lanes 0 and 31
+        // x neighbours across vectors: shuffles inside the warp; lanes 0 and 31 take the scalar at eoff
+        // (the box halo, or the side area when the column beyond is a neighbour's)
         T eu = T(0), ev = T(0);
-        if (XF == 2 && own_x) { eu = gu; ev = gv; }                // ghost from the dense receive buffer
-        else if (lane_w || lane_e) { eu = pu_[eoff]; ev = pv_[eoff]; }
+        if (lane_w || lane_e) { eu = pu_[eoff]; ev = pv_[eoff]; }
         const T su = __shfl_up_sync(0xffffffffu, a0.a[N - 1], 1), sd = __shfl_down_sync(0xffffffffu, a0.a[0], 1);
         const T tu = __shfl_up_sync(0xffffffffu, b0.a[N - 1], 1), td = __shfl_down_sync(0xffffffffu, b0.a[0], 1);
         const T uw = lane_w ? eu : su, ue = lane_e ? eu : sd;
@@ -216,32 +256,38 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, const unsi
             store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
             pou += pxy;
             pov += pxy;
-            if (XF >= 1 && own_x) {                                // my boundary column goes out with the update
-                sp[0] = lane_w ? ou.a[0] : ou.a[N - 1];
-                sp[svoff] = lane_w ? ov.a[0] : ov.a[N - 1];
+            if (XF && own_x) {                                   // my boundary column, for the producer to send
+                pu_[eoff + 2 * TY] = lane_w ? ou.a[0] : ou.a[N - 1];
+                pv_[eoff + 2 * TY] = lane_w ? ov.a[0] : ov.a[N - 1];
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // a bulk copy will read it
             }
         }
     }
 }
 
-// XF: how much of the x faces this instantiation carries itself (XFaceArgs): 0 nothing, 1 it writes
-// its boundary columns into the message buffers (no strided pack), 2 it also reads its x ghosts from
-// the receive buffers (no strided unpack).  Kept apart so that the plain kernel pays neither the
-// registers nor the instructions.
-template <typename T, int ARITH, bool NOISE, int TY, int STAGES, int MINB, int XF>
+// XF = true: the x faces of the halo ride inside this kernel (XFaceArgs; pipelined scheme, sx a whole
+// number of tiles, sy a whole number of 16-byte vectors).  Only the CTAs of the first / last x tile take
+// part, and there the work is the producer's: per plane it fetches the TY ghost values of the W / E
+// neighbour column from the dense receive buffer with a bulk copy into the slot's side area (same mbarrier
+// as the tile), and when a slot comes back from the consumers it sends the TY new boundary values they
+// left there to the dense message buffer with a bulk store.  The consumers pay two predicated shared
+// stores per plane in one lane; the strided pack / unpack kernels (128 bytes of DRAM per 4-byte cell)
+// disappear.
+template <typename T, int ARITH, bool NOISE, int TY, int STAGES, int MINB, bool XF>
 __global__ void __launch_bounds__(32 * (TY + 1), MINB)
 stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_v,
                    T* __restrict__ uo, T* __restrict__ vo, const Layout L, const Params p, const Box box,
                    const int zchunk, const XFaceArgs xf) {
     using Tile = TmaTile<T, TY>;
     constexpr int N = Tile::N;
+    constexpr int FB = Tile::field_bytes(XF), SB = Tile::stage_bytes(XF);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    // carve: [stages][2 fields][FIELD_BYTES] | full[STAGES] | empty[STAGES]; keep the shared address
+    // carve: [stages][2 fields][box | side area] | full[STAGES] | empty[STAGES]; keep the shared address
     // space visible to the compiler (LDS, not generic LD): offset the array, do not round a pointer
     const unsigned pad = (128u - (smem_u32(smem_raw) & 127u)) & 127u;
     unsigned char* tiles = smem_raw + pad;
     const unsigned tiles_u32 = smem_u32(tiles);
-    const unsigned bar0 = tiles_u32 + (unsigned)(STAGES * Tile::STAGE_BYTES);
+    const unsigned bar0 = tiles_u32 + (unsigned)(STAGES * SB);
     auto full_bar = [&](int s) { return bar0 + 8u * (unsigned)s; };
     auto empty_bar = [&](int s) { return bar0 + 8u * (unsigned)(STAGES + s); };
 
@@ -252,6 +298,9 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
     const int zs = box.z0 + blockIdx.z * zchunk;
     const int ze = min(zs + zchunk, box.z1);
     const int nplanes = ze - zs + 2;                     // zs-1 .. ze
+    // does this tile hold a column whose x neighbour belongs to another subdomain?
+    const bool tile_lo = XF && xtile == 0 && xf.send_lo != nullptr;
+    const bool tile_hi = XF && xtile + 32 * N == L.sx && xf.send_hi != nullptr;
 
     if (w == 0 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), TY); }
@@ -265,17 +314,61 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
         if (lane == 0) {
             const int c0 = L.xoff + xtile - N;           // element index in row
             const int c1 = ytile;                        // row index of y = ytile-1
+            // x faces: rows of this tile inside the subdomain, and where plane zs of the piece starts
+            const unsigned xbytes = (unsigned)(min(TY, L.sy - ytile) * (int)sizeof(T));
+            const long long f0 = (long long)ytile + (long long)L.sy * (zs - xf.zbase);   // element (ytile, zs)
+            const long long fv = (long long)L.sy * xf.nz;                                // v part of a piece
             int s = 0;
             unsigned ph = 1;                             // fresh barriers: waiting on parity 1 passes
-            for (int i = 0; i < nplanes; ++i) {
+            // planes 1 .. nplanes-2 are the updated ones; a slot filled at iteration j comes back at j + STAGES
+            const int last = (XF && (tile_lo || tile_hi)) ? nplanes - 2 + STAGES : nplanes - 1;
+            for (int i = 0; i <= last; ++i) {
                 mbar_wait(empty_bar(s), ph);
-                mbar_expect_tx(full_bar(s), 2u * (unsigned)Tile::BOX_BYTES);
-                const unsigned dst = tiles_u32 + (unsigned)(s * Tile::STAGE_BYTES);
-                const int c2 = zs + i;                   // plane index of z = zs-1+i
-                tma_load_3d(dst, &map_u, c0, c1, c2, full_bar(s));
-                tma_load_3d(dst + Tile::FIELD_BYTES, &map_v, c0, c1, c2, full_bar(s));
+                const unsigned slot = tiles_u32 + (unsigned)(s * SB);
+                if (XF && (tile_lo || tile_hi)) {
+                    const int j = i - STAGES;            // the plane this slot held: its new columns are ready
+                    if (j >= 1 && j <= nplanes - 2) {
+                        const long long e = f0 + (long long)L.sy * (j - 1);
+                        const unsigned out_lo = slot + (unsigned)((Tile::BOXR + 2 * TY) * (int)sizeof(T));
+                        const unsigned out_hi = out_lo + (unsigned)(TY * (int)sizeof(T));
+                        if (tile_lo) {
+                            bulk_store_1d((T*)xf.send_lo + e, out_lo, xbytes);
+                            bulk_store_1d((T*)xf.send_lo + e + fv, out_lo + FB, xbytes);
+                        }
+                        if (tile_hi) {
+                            bulk_store_1d((T*)xf.send_hi + e, out_hi, xbytes);
+                            bulk_store_1d((T*)xf.send_hi + e + fv, out_hi + FB, xbytes);
+                        }
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                        // the side area is rewritten only after this slot has been refilled and consumed;
+                        // still, do not refill before the copy has read it
+                        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    }
+                }
+                if (i < nplanes) {
+                    const bool upd = XF && i >= 1 && i <= nplanes - 2;     // ghosts are needed for updated planes only
+                    const unsigned extra = upd ? ((tile_lo ? 2u : 0u) + (tile_hi ? 2u : 0u)) * xbytes : 0u;
+                    mbar_expect_tx(full_bar(s), 2u * (unsigned)Tile::BOX_BYTES + extra);
+                    const int c2 = zs + i;               // plane index of z = zs-1+i
+                    tma_load_3d(slot, &map_u, c0, c1, c2, full_bar(s));
+                    tma_load_3d(slot + FB, &map_v, c0, c1, c2, full_bar(s));
+                    if (upd) {
+                        const long long e = f0 + (long long)L.sy * (i - 1);
+                        const unsigned in_lo = slot + (unsigned)(Tile::BOXR * (int)sizeof(T));
+                        const unsigned in_hi = in_lo + (unsigned)(TY * (int)sizeof(T));
+                        if (tile_lo) {
+                            bulk_load_1d(in_lo, (const T*)xf.ghost_lo + e, xbytes, full_bar(s));
+                            bulk_load_1d(in_lo + FB, (const T*)xf.ghost_lo + e + fv, xbytes, full_bar(s));
+                        }
+                        if (tile_hi) {
+                            bulk_load_1d(in_hi, (const T*)xf.ghost_hi + e, xbytes, full_bar(s));
+                            bulk_load_1d(in_hi + FB, (const T*)xf.ghost_hi + e + fv, xbytes, full_bar(s));
+                        }
+                    }
+                }
                 if (++s == STAGES) { s = 0; ph ^= 1u; }
             }
+            if (XF && (tile_lo || tile_hi)) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
         }
         return;
     }
@@ -290,39 +383,24 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
     T* pov = vo + out0;
     const int roff = (w + 1) * Tile::BW + N + lane * N;  // my centre vector in the box (elements)
     const bool lane_w = lane == 0, lane_e = lane == 31;
-    const int eoff = lane_w ? roff - 1 : roff + N;       // the halo scalar an edge lane needs
+    // the lane that owns column 0 / sx-1 of a row whose x neighbour is another subdomain
+    const bool own_x = XF && ((lane_w && tile_lo) || (lane_e && tile_hi));
+    // the scalar an edge lane needs: the box halo, or the ghost the producer put into the side area
+    const int eoff = own_x ? Tile::BOXR + (lane_w ? 0 : TY) + w : (lane_w ? roff - 1 : roff + N);
 
     Vec<T> ua, ub, uc, va, vb, vc;
 #pragma unroll
     for (int q = 0; q < N; ++q) { ua.a[q] = ub.a[q] = uc.a[q] = va.a[q] = vb.a[q] = vc.a[q] = T(0); }
 
-    // x faces carried by this kernel (XFaceArgs; send_* set, ghost_* set too when XF == 2): only the
-    // lane that owns column 0 / sx-1 of an active row takes part
-    const bool own_lo = lane_w && xtile == 0 && xf.send_lo != nullptr;
-    const bool own_hi = lane_e && xtile + 32 * N == L.sx && xf.send_hi != nullptr;
-    const bool own_x = XF >= 1 && vec_active && (own_lo || own_hi);
-    const int svoff = L.sy * xf.nz;                          // v part of a piece; a piece has < 2^31 elements
-    // element of (y, plane zs) in a piece; addresses are rebuilt from it every iteration instead of
-    // carrying pointers in registers (the plain kernel already sits at its register cap)
-    const int fidx0 = y + L.sy * (zs - xf.zbase);
-    T gu = T(0), gv = T(0);
-
     int s = 0, sprev = 0;
     unsigned ph = 0;
-    // one step of the ring: wait for plane i, consume (plane i-1 is updated), fetch the x ghost the
-    // next iteration needs into the registers the consume has just finished with, release plane i-1
+    // one step of the ring: wait for plane i, consume (plane i-1 is updated), release plane i-1
 #define GSB_TMA_STEP(AM, A0, AP, BM, B0, BP)                                                              \
     {                                                                                                     \
         mbar_wait(full_bar(s), ph);                                                                       \
-        tma_consume<T, ARITH, NOISE, TY, XF>(tiles + s * Tile::STAGE_BYTES, tiles + sprev * Tile::STAGE_BYTES, i, \
-                                         AM, A0, AP, BM, B0, BP, roff, eoff, lane_w, lane_e, vec_active, p, box, x, \
-                                         y, zs + i - 2, pou, pov, L.pxy, own_x, gu, gv,                   \
-                                         (own_lo ? (T*)xf.send_lo : (T*)xf.send_hi) + (fidx0 + L.sy * (i - 2)), svoff); \
-        if (XF == 2 && own_x && (unsigned)(i - 1) < (unsigned)(ze - zs)) {                                \
-            const T* gp = (own_lo ? (const T*)xf.ghost_lo : (const T*)xf.ghost_hi) + (fidx0 + L.sy * (i - 1)); \
-            gu = gp[0];                                 /* ghost of plane zs + i - 1, used next iteration */ \
-            gv = gp[svoff];                                                                               \
-        }                                                                                                 \
+        tma_consume<T, ARITH, NOISE, TY, XF>(tiles + s * SB, tiles + sprev * SB, i, AM, A0, AP, BM, B0, BP, roff, eoff, \
+                                             lane_w, lane_e, vec_active, p, box, x, y, zs + i - 2, pou, pov, L.pxy,  \
+                                             own_x);                                                      \
         if (i >= 1) {                                                                                     \
             __syncwarp();                                                                                 \
             if (lane == 0) mbar_arrive(empty_bar(sprev));                                                 \
@@ -372,7 +450,7 @@ naive_reflayout_kernel(const T* __restrict__ u, const T* __restrict__ v, T* __re
     if constexpr (ARITH == ARITH_NATIVE) {
         cell_update_native<NOISE>(uc, vc, su, sv, NOISE ? noise_r32(word) : 0.f, p, un, vn);
     } else {
-        cell_update_ref<NOISE>(uc, vc, su, sv, NOISE ? noise_r64(word) : 0.0, p, un, vn);
+        cell_update_ref<NOISE, REF_GENERIC>(uc, vc, su, sv, NOISE ? noise_r64(word) : 0.0, p, un, vn);
     }
     uo[c] = un;
     vo[c] = vn;

@@ -122,7 +122,8 @@ struct gsb_handle {
     // asynchronous output (gsb_get_fields_async): device snapshot + D2H on its own stream
     cudaStream_t s_copy;
     cudaEvent_t ev_snap, ev_copied;
-    void* stage[2];          // contiguous ghost-free copies of u and v (allocated on first use)
+    void* stage[2];          // two contiguous staging buffers of one ghosted field each (allocated on first use)
+    bool stage_failed;       // the allocation was tried and did not fit
     bool copy_in_flight;
     cudaEvent_t ev_compute, ev_halo, ev_packed, ev_chunk;
     cudaEvent_t ev_piece[GSB_MAX_CHUNKS];   // pipelined halo: piece k of the previous step has landed
@@ -184,6 +185,7 @@ static Params make_params(const gsb_handle* h) {
     }
     p.noise_s = ldexp(p.noise, -31);
     p.noise_fast = p.noise == 0.0 || (std::isnormal(p.noise_s) && ldexp(p.noise_s, 31) == p.noise);
+    p.ref_mode = !p.noise_fast ? 2 : (p.dt_is_one ? 0 : 1);
     p.fDu6 = p.fDu / 6.0f;
     p.fDv6 = p.fDv / 6.0f;
     p.fnoise_s = ldexpf(p.fnoise, -23);
@@ -225,19 +227,21 @@ static bool kernel_shape_ok(const StencilCfg& k) {
                : (k.ty == 4 || k.ty == 8);
 }
 
-// Measured best shapes on B200 (profiles/r1_tuning.md): occupancy class, rows per CTA, ring depth,
+// Measured best shapes on B200 (profiles/r1_tuning_raw.log, profiles/r2_tuning_raw.log): occupancy class, rows per CTA, ring depth,
 // planes per CTA; small grids get shorter z chunks so that every SM still holds several CTAs.
 static void default_kernel(gsb_handle* h) {
     StencilCfg& k = h->kcfg;
     const bool nz = k.noise != 0;
     if (k.dtype == DT_F64) {
-        k.kind = KERNEL_TMA_LO; k.ty = 8;
-        if (nz) { k.stages = 4; k.zchunk = 64; } else { k.stages = 6; k.zchunk = 32; }
+        k.kind = KERNEL_TMA_LO;
+        if (nz) { k.ty = 4; k.stages = 4; k.zchunk = 32; } else { k.ty = 8; k.stages = 6; k.zchunk = 32; }
     } else if (k.arith == ARITH_NATIVE) {
         k.kind = KERNEL_TMA_HI; k.ty = 8;
         if (nz) { k.stages = 6; k.zchunk = 32; } else { k.stages = 4; k.zchunk = 16; }
     } else {
-        k.kind = KERNEL_TMA_HI; k.ty = 8; k.stages = 4; k.zchunk = 64;
+        // Float32 reference arithmetic (FP64-pipe and conversion bound): the lower occupancy class, no spills
+        k.kind = KERNEL_TMA_LO;
+        if (nz) { k.ty = 8; k.stages = 4; k.zchunk = 64; } else { k.ty = 4; k.stages = 8; k.zchunk = 64; }
     }
     // small grids: more, smaller CTAs (measured at L = 256: 4 rows per CTA beats 8 by 6 %)
     if ((long long)h->L.sx * h->L.sy * h->L.sz <= 300ll * 300 * 300 && (k.dtype == DT_F64 || k.arith == ARITH_NATIVE)) {
@@ -404,7 +408,7 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
         const char* hc = getenv("GSB_HALO_CHUNKS");
         h->halo_chunks = hc ? atoi(hc) : 0;
         const char* fx = getenv("GSB_FUSE_X");
-        h->fuse_x = fx ? atoi(fx) : 0;
+        h->fuse_x = fx ? atoi(fx) : 2;
     }
     for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&h->tev[i]));
     for (int k = 0; k <= GSB_MAX_CHUNKS; ++k)
@@ -467,21 +471,64 @@ extern "C" int gsb_sync(gsb_t* h) {
     return 0;
 }
 
-// strided copy between the padded device array and a dense host array (g = 1: with ghosts)
-static int copy_field(gsb_handle* h, void* dev, void* host, int g, bool to_host) {
+// Two contiguous staging buffers of one GHOSTED field each, allocated on first use.  Host transfers go
+// through them: one dense cudaMemcpyAsync at full PCIe rate plus a strided device-to-device copy (a few
+// ms at L = 1024) instead of one strided host copy (measured: 41-44 GB/s strided against >50 dense).
+// Returns false when the memory is not there (L = 2048 on one GPU): callers then copy strided.
+static bool ensure_stage(gsb_handle* h) {
+    if (h->stage[0] && h->stage[1]) return true;
+    if (h->stage_failed) return false;
+    const Layout& L = h->L;
+    const size_t bytes = (size_t)(L.sx + 2) * (size_t)(L.sy + 2) * (size_t)(L.sz + 2) * h->es;
+    for (int i = 0; i < 2; ++i)
+        if (!h->stage[i] && cudaMalloc(&h->stage[i], bytes) != cudaSuccess) {
+            cudaGetLastError();
+            for (int q = 0; q < 2; ++q) if (h->stage[q]) { cudaFree(h->stage[q]); h->stage[q] = nullptr; }
+            h->stage_failed = true;
+            return false;
+        }
+    return true;
+}
+
+// strided copy between the padded device array and a dense array `other` (g = 1: with ghosts) that lives
+// on the host (kind H2D / D2H) or on the device (D2D: the staging buffers)
+static int copy_strided(gsb_handle* h, void* dev, void* other, int g, bool from_dev, cudaMemcpyKind kind, cudaStream_t st) {
     const Layout& L = h->L;
     cudaMemcpy3DParms p;
     memset(&p, 0, sizeof p);
     const size_t nx = (size_t)(L.sx + 2 * g), ny = (size_t)(L.sy + 2 * g), nz = (size_t)(L.sz + 2 * g);
     // no CUDA array takes part: every x quantity is in bytes
     cudaPitchedPtr dptr = make_cudaPitchedPtr(dev, (size_t)L.px * h->es, (size_t)L.px * h->es, (size_t)(L.sy + 2));
-    cudaPitchedPtr hptr = make_cudaPitchedPtr(host, nx * h->es, nx * h->es, ny);
+    cudaPitchedPtr optr = make_cudaPitchedPtr(other, nx * h->es, nx * h->es, ny);
     cudaPos dpos = make_cudaPos((size_t)(L.xoff - g) * h->es, (size_t)(1 - g), (size_t)(1 - g));
-    cudaPos hpos = make_cudaPos(0, 0, 0);
+    cudaPos opos = make_cudaPos(0, 0, 0);
     p.extent = make_cudaExtent(nx * h->es, ny, nz);
-    if (to_host) { p.srcPtr = dptr; p.srcPos = dpos; p.dstPtr = hptr; p.dstPos = hpos; p.kind = cudaMemcpyDeviceToHost; }
-    else { p.srcPtr = hptr; p.srcPos = hpos; p.dstPtr = dptr; p.dstPos = dpos; p.kind = cudaMemcpyHostToDevice; }
-    CK(cudaMemcpy3DAsync(&p, h->s_compute));
+    if (from_dev) { p.srcPtr = dptr; p.srcPos = dpos; p.dstPtr = optr; p.dstPos = opos; }
+    else { p.srcPtr = optr; p.srcPos = opos; p.dstPtr = dptr; p.dstPos = dpos; }
+    p.kind = kind;
+    CK(cudaMemcpy3DAsync(&p, st));
+    return 0;
+}
+
+// padded device array <-> dense host array, on the update stream; `slot` picks the staging buffer
+static int copy_field(gsb_handle* h, void* dev, void* host, int g, bool to_host, int slot = 0) {
+    const Layout& L = h->L;
+    const size_t bytes = (size_t)(L.sx + 2 * g) * (size_t)(L.sy + 2 * g) * (size_t)(L.sz + 2 * g) * h->es;
+    // small fields: one strided copy has the lower latency
+    if (bytes < ((size_t)8 << 20) || !ensure_stage(h))
+        return copy_strided(h, dev, host, g, to_host, to_host ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice, h->s_compute);
+    if (h->copy_in_flight) {                                 // an asynchronous output still drains from the buffers
+        CK(cudaEventSynchronize(h->ev_copied));
+        h->copy_in_flight = false;
+    }
+    void* stg = h->stage[slot & 1];
+    if (to_host) {
+        if (copy_strided(h, dev, stg, g, true, cudaMemcpyDeviceToDevice, h->s_compute)) return 1;
+        CK(cudaMemcpyAsync(host, stg, bytes, cudaMemcpyDeviceToHost, h->s_compute));
+    } else {
+        CK(cudaMemcpyAsync(stg, host, bytes, cudaMemcpyHostToDevice, h->s_compute));
+        if (copy_strided(h, dev, stg, g, false, cudaMemcpyDeviceToDevice, h->s_compute)) return 1;
+    }
     return 0;
 }
 
@@ -492,8 +539,8 @@ extern "C" int gsb_get_fields(gsb_t* h, void* u_host, void* v_host) {
     DeviceGuard guard_(h->device);
     if (guard_.err != cudaSuccess) return fail("cudaSetDevice(%d) -> %s", h->device, cudaGetErrorString(guard_.err));
     CK(cudaStreamSynchronize(h->s_comm));
-    if (copy_field(h, h->f[0], u_host, 0, true)) return 1;
-    if (copy_field(h, h->f[1], v_host, 0, true)) return 1;
+    if (copy_field(h, h->f[0], u_host, 0, true, 0)) return 1;
+    if (copy_field(h, h->f[1], v_host, 0, true, 1)) return 1;
     CK(cudaStreamSynchronize(h->s_compute));
     return 0;
 }
@@ -519,16 +566,7 @@ extern "C" int gsb_get_fields_async(gsb_t* h, void* u_host, void* v_host) {
     const Layout& L = h->L;
     const size_t nx = (size_t)L.sx, ny = (size_t)L.sy, nz = (size_t)L.sz;
     const size_t bytes = nx * ny * nz * h->es;
-    for (int i = 0; i < 2; ++i)
-        if (!h->stage[i]) {
-            cudaError_t e = cudaMalloc(&h->stage[i], bytes);
-            if (e != cudaSuccess) {                 // no room for a snapshot (L = 2048 on one GPU): plain get
-                cudaGetLastError();
-                if (i == 1) { cudaFree(h->stage[0]); h->stage[0] = nullptr; }
-                h->stage[i] = nullptr;
-                return gsb_get_fields(h, u_host, v_host);
-            }
-        }
+    if (!ensure_stage(h)) return gsb_get_fields(h, u_host, v_host);   // no room for a snapshot (L = 2048 on one GPU)
     if (gsb_output_wait(h)) return 1;               // the staging buffers are free again
     void* host[2] = {u_host, v_host};
     for (int i = 0; i < 2; ++i) {
@@ -829,19 +867,17 @@ static bool interior_box(const gsb_handle* h, Box* b) {
     return true;
 }
 
-// Optional ($GSB_FUSE_X=1|2 at gsb_create): the x faces ride inside the update kernel (XFaceArgs) when the
-// pipelined scheme runs the TMA kernel on a subdomain whose sx is a whole number of tiles.  It removes
-// the strided pack/unpack of 2 * sy * sz cells (~0.1 ms per step at 1024^3), but the XF instantiation
-// of the kernel runs against the register cap (spills, re-materialised indices) and loses more than
-// that (measured per step, two subdomains of 1024^3: 3.21 vs 3.05 ms without noise, 3.62 vs 3.18 ms
-// with), so it is OFF by default; kept because it is bit-exact and tested.
-// Returns 0 (off), 1 (the kernel writes the x messages: no strided pack) or 2 (it also reads the x ghosts
-// from the receive buffers: no strided unpack).
-static int fused_x(const gsb_handle* h) {
+// The x faces ride inside the update kernel (XFaceArgs, gs_stencil.cuh) when the pipelined scheme runs
+// the TMA kernel on a subdomain whose sx is a whole number of tiles and whose sy is a whole number of
+// 16-byte vectors: the producer warps of the first / last x tile fetch the neighbour's column from the
+// dense receive buffer and send the new boundary column to the dense message buffer with bulk copies.
+// That removes the strided pack / unpack of 2 * sy * sz cells (a 128-byte DRAM line per 4-byte cell).
+// $GSB_FUSE_X at gsb_create: 2 (default) the x-face instantiation runs on the first / last x tile only,
+// 1 on the whole chunk, 0 off (the strided kernels then carry the x faces as well).
+static bool fused_x(const gsb_handle* h) {
     const int tile = 32 * (int)(16 / h->es);
-    const bool can = h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
-                     (h->active[GSB_WEST] || h->active[GSB_EAST]) && h->L.sx % tile == 0;
-    return can ? (h->fuse_x >= 2 ? 2 : h->fuse_x == 1 ? 1 : 0) : 0;
+    return h->fuse_x != 0 && h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
+           (h->active[GSB_WEST] || h->active[GSB_EAST]) && h->L.sx % tile == 0 && h->L.sy % (int)(16 / h->es) == 0;
 }
 
 // A piece of the halo: which faces travel, and for the x / y faces which z range.
@@ -1033,11 +1069,11 @@ static XFaceArgs chunk_xface(const gsb_handle* h, int k, int C) {
     const int rd = (int)(h->step & 1), wr = (int)((h->step + 1) & 1);
     auto at = [&](void* base, int d) { return (void*)((char*)base + piece_offset(h, d, pc.z0)); };
     if (h->active[GSB_WEST]) {
-        if (fused_x(h) == 2) xf.ghost_lo = at(h->recv[rd][GSB_WEST], GSB_WEST);
+        xf.ghost_lo = at(h->recv[rd][GSB_WEST], GSB_WEST);
         xf.send_lo = at(h->transport == TR_LOCAL ? h->peer[GSB_WEST]->recv[wr][GSB_EAST] : h->send[GSB_WEST], GSB_WEST);
     }
     if (h->active[GSB_EAST]) {
-        if (fused_x(h) == 2) xf.ghost_hi = at(h->recv[rd][GSB_EAST], GSB_EAST);
+        xf.ghost_hi = at(h->recv[rd][GSB_EAST], GSB_EAST);
         xf.send_hi = at(h->transport == TR_LOCAL ? h->peer[GSB_EAST]->recv[wr][GSB_WEST] : h->send[GSB_EAST], GSB_EAST);
     }
     return xf;
@@ -1058,10 +1094,31 @@ static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, 
     if (i == 1) CK(cudaStreamWaitEvent(h->s_compute2, h->ev_compute, 0));   // previous step is complete
     if (h->n_active) CK(cudaStreamWaitEvent(st, h->ev_piece[chunk_dependency(k, C)], 0));
     const Piece pc = chunk_piece(h, k, C);
+    const int sx = h->L.sx, sy = h->L.sy;
     if (fused_x(h)) {
         const XFaceArgs xf = chunk_xface(h, k, C);
-        if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p, st, &xf)) return 1;
-    } else if (launch_box(h, Box{0, h->L.sx, 0, h->L.sy, pc.z0, pc.z1}, p, st)) return 1;
+        const int tile = 32 * (int)(16 / h->es);
+        if (h->fuse_x == 1 || sx <= tile) {
+            // one launch, every CTA runs the x-face instantiation (only the edge tiles act on it)
+            if (launch_box(h, Box{0, sx, 0, sy, pc.z0, pc.z1}, p, st, &xf)) return 1;
+        } else {
+            // the x-face instantiation on the first / last x tile only, the plain kernel in between: where
+            // the former is slower (it spills at the register cap of the noisy variants) it now touches
+            // 1/8 .. 2/8 of the cells instead of all of them
+            int lo = 0, hi = sx;
+            if (xf.send_lo) {
+                XFaceArgs a = xf; a.send_hi = nullptr; a.ghost_hi = nullptr;
+                if (launch_box(h, Box{0, tile, 0, sy, pc.z0, pc.z1}, p, st, &a)) return 1;
+                lo = tile;
+            }
+            if (xf.send_hi) {
+                XFaceArgs a = xf; a.send_lo = nullptr; a.ghost_lo = nullptr;
+                if (launch_box(h, Box{sx - tile, sx, 0, sy, pc.z0, pc.z1}, p, st, &a)) return 1;
+                hi = sx - tile;
+            }
+            if (hi > lo) if (launch_box(h, Box{lo, hi, 0, sy, pc.z0, pc.z1}, p, st)) return 1;
+        }
+    } else if (launch_box(h, Box{0, sx, 0, sy, pc.z0, pc.z1}, p, st)) return 1;
     CK(cudaEventRecord(h->ev_chunk, st));
     if (last) {
         if (C > 1) {                                             // join the second stream into the first
@@ -1097,7 +1154,7 @@ static int pipeline_prime(gsb_handle** hs, int n) {
         for (int r = 0; r < n; ++r) {
             gsb_handle* h = hs[r];
             if (h->n_active)
-                if (enqueue_unpack(h, chunk_piece(h, k, C), 0, (int)(h->step & 1), h->ev_piece[k], fused_x(h) == 2)) return 1;
+                if (enqueue_unpack(h, chunk_piece(h, k, C), 0, (int)(h->step & 1), h->ev_piece[k], fused_x(h))) return 1;
         }
     }
     for (int r = 0; r < n; ++r) if (hs[r]->n_active) {
@@ -1112,7 +1169,7 @@ static int pipeline_prime(gsb_handle** hs, int n) {
 // Array(fields.u) must show the neighbours' columns although, in the fused scheme, the kernels read
 // them from the receive buffers: copy them into the ghost columns of the current fields on demand.
 static int refresh_x_ghosts(gsb_handle* h) {
-    if (!h->n_active || !h->ghost_valid || fused_x(h) != 2) return 0;
+    if (!h->n_active || !h->ghost_valid || !fused_x(h)) return 0;
     const int C = pipeline_chunks(h);
     for (int k = 0; k < C; ++k) {
         Piece pc = chunk_piece(h, k, C);
@@ -1146,12 +1203,12 @@ static int pipeline_step(gsb_handle** hs, int n) {
             gsb_handle* h = hs[r];
             if (pipeline_compute_chunk(h, k, C, ps[r], i)) return 1;
             if (h->n_active)
-                if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk, fused_x(h) >= 1)) return 1;
+                if (enqueue_pack_send(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_chunk, fused_x(h))) return 1;
         }
         for (int r = 0; r < n; ++r) {
             gsb_handle* h = hs[r];
             if (h->n_active)
-                if (enqueue_unpack(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_piece[k], fused_x(h) == 2)) return 1;
+                if (enqueue_unpack(h, chunk_piece(h, k, C), 1, (int)((h->step + 1) & 1), h->ev_piece[k], fused_x(h))) return 1;
         }
     }
     for (int r = 0; r < n; ++r) { swap_bindings(hs[r]); hs[r]->ghost_valid = hs[r]->n_active > 0; }
@@ -1192,7 +1249,7 @@ extern "C" int gsb_calculate(gsb_t* h) {
         CK(cudaStreamWaitEvent(h->s_compute, h->ev_halo, 0));
         CK(cudaStreamWaitEvent(h->s_compute2, h->ev_halo, 0));
     }
-    if (h->n_active && fused_x(h) == 2 && h->ghost_valid) if (refresh_x_ghosts(h)) return 1;
+    if (h->n_active && fused_x(h) && h->ghost_valid) if (refresh_x_ghosts(h)) return 1;
     if (launch_box(h, full_box(h), p)) return 1;
     CK(cudaEventRecord(h->ev_compute, h->s_compute));
     return 0;

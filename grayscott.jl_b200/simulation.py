@@ -169,6 +169,11 @@ class Fields:
     def set_kernel(self, kind=-1, ty=0, stages=0, zchunk=0):
         check(lib().gsb_set_kernel(self._h, kind, ty, stages, zchunk))
 
+    def get_kernel(self):
+        k = [C.c_int() for _ in range(4)]
+        check(lib().gsb_get_kernel(self._h, *[C.byref(x) for x in k]))
+        return tuple(x.value for x in k)
+
     def timers_enable(self, on=True):
         check(lib().gsb_timers_enable(self._h, int(on)))
 

@@ -475,22 +475,24 @@ def test_halo_exchange_other_decompositions(sim, orc, monkeypatch, nranks, L, sc
 
 
 @pytest.mark.parametrize("prec", ["Float32", "Float64"])
-@pytest.mark.parametrize("nranks", [2, 4, 8])
+@pytest.mark.parametrize("nranks,L", [(2, 256), (4, 256), (8, 256), (3, 384)])
 @pytest.mark.parametrize("chunks", [None, 1, 3])
-@pytest.mark.parametrize("level", [1, 2])
-def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nranks, chunks, level):
-    """Optional scheme (GSB_FUSE_X=1|2): sx = 128 is a whole number of tiles, so the update kernel can
-    write its boundary columns into the message buffers (level 1: no strided pack) and also read its x
-    ghosts from the receive buffers (level 2: no strided unpack either).  Must equal the oracle's N-rank run bit for bit, and Array(fields.u) must
-    still show the neighbour's column in the ghost layer."""
+@pytest.mark.parametrize("fuse", [2, 1, 0])
+def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nranks, L, chunks, fuse):
+    """sx = 128 is a whole number of tiles, so the update kernel carries the x faces itself (default;
+    GSB_FUSE_X=0 switches back to the strided pack / unpack kernels): the producer warps of the first / last
+    x tile fetch the neighbour's column from the dense receive buffer and send the new boundary column with
+    bulk copies.  With 3 ranks along x (Float32: one tile per rank) the middle rank's CTAs own both sides.
+    Must equal the oracle's N-rank run bit for bit, and Array(fields.u) must still show the neighbour's
+    column in the ghost layer."""
     monkeypatch.setenv("GSB_HALO", "pipeline")
-    monkeypatch.setenv("GSB_FUSE_X", str(level))
-    monkeypatch.setenv("GSB_KERNEL", "tma:8:4:16")      # the fused variants exist for the TMA kernel only
+    monkeypatch.setenv("GSB_FUSE_X", str(fuse))
+    monkeypatch.setenv("GSB_KERNEL", "tma:8:4:16")      # the fused variant exists for the TMA kernel only
     if chunks:
         monkeypatch.setenv("GSB_HALO_CHUNKS", str(chunks))
     else:
         monkeypatch.delenv("GSB_HALO_CHUNKS", raising=False)
-    L, steps = 256, 7
+    steps = 7
     s = settings(sim, L, prec, 0.1)
     ranks = []
     for r in range(nranks):
@@ -498,8 +500,10 @@ def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nrank
         ranks.append((mcd, sim.init_fields(s, mcd, prec, seed=13)))
     assert ranks[0][0].proc_sizes[0] == 128
     sim.connect_local([f for _, f in ranks])
+    launches0 = ranks[0][1].launch_count()
     sim.iterate_group([f for _, f in ranks], s, nsteps=3)
     sim.iterate_group([f for _, f in ranks], s, nsteps=steps - 3)
+    per_step = (ranks[0][1].launch_count() - launches0) / steps
     o = orc.Oracle(L, prec, dims=orc.dims_create(nranks), noise=0.1, seed=13, **PHYS)
     o.step(steps)
     got = []
@@ -513,6 +517,10 @@ def test_x_faces_carried_by_the_update_kernel(sim, orc, monkeypatch, prec, nrank
     east = mcd0.proc_neighbors["east"]
     g = np.asarray(f0.u)
     assert np.array_equal(g[1:-1, 1:-1, -1], got[east][:, :, 0])
+    if nranks in (2, 3) and fuse:
+        # only x faces exist: no pack / unpack kernel at all after the first (priming) exchange
+        C_ = chunks or (4 if ranks[0][0].proc_sizes[2] >= 192 else 2)
+        assert per_step <= (1 if fuse == 1 else 3) * C_ + 2 * C_ / steps + 1e-9, per_step
     for _, f in ranks:
         f.close()
 

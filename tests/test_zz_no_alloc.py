@@ -71,6 +71,8 @@ def test_noalloc_rejects_fields_beyond_the_builtin_scratch(pkg):
     assert rc != 0 and "GSB_NOALLOC_MAX_PLANES" in msg and "4096" in msg
     rc, msg = call_noalloc(pkg, 7, (4, 4, 4), dummy, 0.0, out)
     assert rc != 0 and "dtype" in msg
+    # like every other entry point, the reason is also what gsb_last_error() returns (a caller may pass no errbuf)
+    assert pkg._lib.lib().gsb_last_error().decode() == msg
 
 
 def test_noalloc_ragged_box(pkg):

@@ -12,10 +12,12 @@
 constexpr int ITERS = 2048;
 constexpr int CHAINS = 8;
 
-enum Op { DFMA, DADD, DMUL, F2D, D2F, I2D, FFMA_, IMADW, LOP, MIX_DFMA_FFMA, MIX_DFMA_F2D, MIX_DFMA_I2D, MIX_F2D_D2F, MAGIC_I2D, DSETP_SEL, NOPS };
+enum Op { DFMA, DADD, DMUL, F2D, D2F, I2D, FFMA_, IMADW, LOP, MIX_DFMA_FFMA, MIX_DFMA_F2D, MIX_DFMA_I2D, MIX_F2D_D2F, MAGIC_I2D, DSETP_SEL, BASE_DFMA_FADD, PLUS_NARROW, PLUS_WIDEN, PLUS_I2D, PLUS_MAGIC, NOPS };
 static const char* kNames[] = {"DFMA", "DADD", "DMUL", "F2F.F64.F32 (widen)", "F2F.F32.F64 (narrow)", "I2F.F64.S32", "FFMA",
                                "IMAD.WIDE.U32", "LOP3", "DFMA + FFMA (1:1)", "DFMA + widen (1:1)", "DFMA + I2F.F64 (1:1)",
-                               "widen + narrow (1:1)", "magic int->double (MOV+DADD)", "DSETP + 2 FSEL"};
+                               "widen + narrow (1:1)", "magic int->double (MOV+DADD)", "DSETP + 2 FSEL",
+                               "DFMA + FADD (baseline)", "DFMA + FADD + narrow(d)", "DFMA(+widen(f)) + FADD", "DFMA(+I2F.F64(u)) + FADD + LOP3",
+                               "DFMA(+magic(u): DADD) + FADD + LOP3"};
 
 template <int OP>
 __global__ void __launch_bounds__(1024) k(long long* cycles, double* sink, int seed) {
@@ -44,6 +46,12 @@ __global__ void __launch_bounds__(1024) k(long long* cycles, double* sink, int s
             if (OP == MIX_DFMA_I2D) { double w; asm volatile("cvt.rn.f64.s32 %0, %1;" : "=d"(w) : "r"(u[c])); asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[c]) : "d"(da), "d"(w)); }
             if (OP == MIX_F2D_D2F) { double w; asm volatile("cvt.f64.f32 %0, %1;" : "=d"(w) : "f"(f[c])); asm volatile("cvt.rn.f32.f64 %0, %1;" : "=f"(f[c]) : "d"(w)); }
             if (OP == MAGIC_I2D) { double w = __hiloint2double(0x43300000, (int)u[c]); asm volatile("add.rn.f64 %0, %1, %2;" : "=d"(d[c]) : "d"(w), "d"(-4503601774854144.0)); asm volatile("" : "+r"(u[c])); }
+            // loop-carried variants: every conversion feeds the next iteration, nothing can be dropped
+            if (OP == BASE_DFMA_FADD) { asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[c]) : "d"(da), "d"(db)); asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(f[c]) : "f"(1e-6f)); }
+            if (OP == PLUS_NARROW) { float t; asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[c]) : "d"(da), "d"(db)); asm volatile("cvt.rn.f32.f64 %0, %1;" : "=f"(t) : "d"(d[c])); asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(f[c]) : "f"(t)); }
+            if (OP == PLUS_WIDEN) { double w; asm volatile("cvt.f64.f32 %0, %1;" : "=d"(w) : "f"(f[c])); asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[c]) : "d"(da), "d"(w)); asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(f[c]) : "f"(1e-6f)); }
+            if (OP == PLUS_I2D) { double w; asm volatile("cvt.rn.f64.s32 %0, %1;" : "=d"(w) : "r"(u[c])); asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[c]) : "d"(da), "d"(w)); asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(f[c]) : "f"(1e-6f)); asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(u[c]) : "r"(0x9E3779B9u), "r"(i)); }
+            if (OP == PLUS_MAGIC) { double w = __hiloint2double(0x43300000, (int)u[c]); asm volatile("add.rn.f64 %0, %0, %1;" : "+d"(w) : "d"(-4503601774854144.0)); asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[c]) : "d"(da), "d"(w)); asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(f[c]) : "f"(1e-6f)); asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(u[c]) : "r"(0x9E3779B9u), "r"(i)); }
             if (OP == DSETP_SEL) { d[c] = (d[c] == db) ? da : d[c]; asm volatile("" : "+d"(d[c])); }
         }
     }
@@ -81,5 +89,8 @@ int main() {
     run<FFMA_>(sms, dc, ds, 1); run<IMADW>(sms, dc, ds, 1); run<LOP>(sms, dc, ds, 1);
     run<MIX_DFMA_FFMA>(sms, dc, ds, 2); run<MIX_DFMA_F2D>(sms, dc, ds, 2); run<MIX_DFMA_I2D>(sms, dc, ds, 2);
     run<MIX_F2D_D2F>(sms, dc, ds, 2); run<MAGIC_I2D>(sms, dc, ds, 1); run<DSETP_SEL>(sms, dc, ds, 1);
+    printf("# loop-carried groups: clk per GROUP per scheduler is what to compare\n");
+    run<BASE_DFMA_FADD>(sms, dc, ds, 1); run<PLUS_NARROW>(sms, dc, ds, 1); run<PLUS_WIDEN>(sms, dc, ds, 1);
+    run<PLUS_I2D>(sms, dc, ds, 1); run<PLUS_MAGIC>(sms, dc, ds, 1);
     return 0;
 }
