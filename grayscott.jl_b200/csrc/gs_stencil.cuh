@@ -52,6 +52,12 @@ __device__ __forceinline__ void update_cells(const Vec<T>& um, const Vec<T>& u0,
 }
 
 template <typename T, int ARITH, bool NOISE>
+__device__ __forceinline__ void update_vec_w(const Vec<T>& um, const Vec<T>& u0, const Vec<T>& up, const Vec<T>& us,
+                                             const Vec<T>& un, T uw, T ue, const Vec<T>& vm, const Vec<T>& v0,
+                                             const Vec<T>& vp, const Vec<T>& vs, const Vec<T>& vn, T vw, T ve,
+                                             const Params& p, const unsigned (&words)[Vec<T>::N], Vec<T>& uo, Vec<T>& vo);
+
+template <typename T, int ARITH, bool NOISE>
 __device__ __forceinline__ void update_vec(const Vec<T>& um, const Vec<T>& u0, const Vec<T>& up,
                                            const Vec<T>& us, const Vec<T>& un, T uw, T ue,
                                            const Vec<T>& vm, const Vec<T>& v0, const Vec<T>& vp,
@@ -59,11 +65,36 @@ __device__ __forceinline__ void update_vec(const Vec<T>& um, const Vec<T>& u0, c
                                            const Params& p, int x, int y, int z, Vec<T>& uo, Vec<T>& vo) {
     constexpr int N = Vec<T>::N;
     unsigned words[N];
+    if constexpr (NOISE) {
+        noise_words<N>(p, (unsigned)(p.gx0 + x), (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), words);
+    } else {
 #pragma unroll
-    for (int i = 0; i < N; ++i) words[i] = 0u;
-    if (NOISE) noise_words<N>(p, (unsigned)(p.gx0 + x), (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), words);
+        for (int i = 0; i < N; ++i) words[i] = 0u;
+    }
+    update_vec_w<T, ARITH, NOISE>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, words, uo, vo);
+}
+
+// the same with the noise words of the N cells supplied by the caller
+template <typename T, int ARITH, bool NOISE>
+__device__ __forceinline__ void update_vec_w(const Vec<T>& um, const Vec<T>& u0, const Vec<T>& up,
+                                             const Vec<T>& us, const Vec<T>& un, T uw, T ue,
+                                             const Vec<T>& vm, const Vec<T>& v0, const Vec<T>& vp,
+                                             const Vec<T>& vs, const Vec<T>& vn, T vw, T ve,
+                                             const Params& p, const unsigned (&words)[Vec<T>::N], Vec<T>& uo, Vec<T>& vo) {
+    constexpr int N = Vec<T>::N;
     if constexpr (ARITH == ARITH_NATIVE) {
-        update_cells<T, ARITH, NOISE, REF_DT1>(um, u0, up, us, un, uw, ue, vm, v0, vp, vs, vn, vw, ve, p, words, uo, vo);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            const T uW = i == 0 ? uw : u0.a[i == 0 ? 0 : i - 1];
+            const T uE = i == N - 1 ? ue : u0.a[i == N - 1 ? i : i + 1];
+            const T vW = i == 0 ? vw : v0.a[i == 0 ? 0 : i - 1];
+            const T vE = i == N - 1 ? ve : v0.a[i == N - 1 ? i : i + 1];
+            const T su = sum6(uW, uE, us.a[i], un.a[i], um.a[i], up.a[i]);
+            const T sv = sum6(vW, vE, vs.a[i], vn.a[i], vm.a[i], vp.a[i]);
+            float r32 = 0.f;
+            if (NOISE) r32 = noise_r32(words[i]);
+            cell_update_native<NOISE>(u0.a[i], v0.a[i], su, sv, r32, p, uo.a[i], vo.a[i]);
+        }
     } else {
         // warp-uniform: one variant of the reference arithmetic for the whole vector
         if (p.ref_mode == REF_DT1)
@@ -168,6 +199,13 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// One arrival per (converged) warp: elect.sync picks the lane, no lane-id test, no separate warp barrier.
+__device__ __forceinline__ void mbar_arrive_one_per_warp(unsigned bar) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "@p mbarrier.arrive.shared::cta.b64 _, [%0];\n\t}" ::"r"(bar) : "memory");
+}
 // The suspend-time hint lets the hardware park the warp instead of re-issuing the poll: without it a
 // waiting consumer warp spent 11-22 issue slots per plane on PHASECHK / BRA / YIELD (ncu source
 // page, round 1), slots the computing warps of the instruction-bound variants need.
@@ -229,7 +267,8 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, unsigned c
                                             const Vec<T>& b0, Vec<T>& bp, const int roff, const int eoff,
                                             const bool lane_w, const bool lane_e, const bool vec_active,
                                             const Params& p, const Box& box, const int x, const int y, const int z,
-                                            T*& pou, T*& pov, const long long pxy, const bool own_x) {
+                                            T*& pou, T*& pov, const long long pxy, const bool own_x,
+                                            const bool pair_ok, unsigned& keep0, unsigned& keep1) {
     using Tile = TmaTile<T, TY>;
     constexpr int N = Tile::N;
     constexpr int FB = Tile::field_bytes(XF);
@@ -250,9 +289,39 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, unsigned c
         const T tu = __shfl_up_sync(0xffffffffu, b0.a[N - 1], 1), td = __shfl_down_sync(0xffffffffu, b0.a[0], 1);
         const T uw = lane_w ? eu : su, ue = lane_e ? eu : sd;
         const T vw = lane_w ? ev : tu, ve = lane_e ? ev : td;
+        // Float64 with noise: a thread owns two cells but a Philox call yields four words.  Two lanes that
+        // share a counter block (4-aligned global x) share the work across TWO planes: on even iterations
+        // the even lane evaluates the block of this plane, the odd lane the block of the next one, and they
+        // swap the halves the other needs; on odd iterations both use what they kept.  Same words as
+        // noise_words (any alignment), half the generator work per cell.
+        constexpr bool PAIR = NOISE && sizeof(T) == 8;
+        unsigned nw[N];
+        if constexpr (PAIR) {
+            if (pair_ok) {
+                const bool odd = (threadIdx.x & 1) != 0;
+                if ((i & 1) == 0) {
+                    const Philox4 blk = philox4x32_10((unsigned)(p.gx0 + x) >> 2, (unsigned)(p.gy0 + y),
+                                                      (unsigned)(p.gz0 + z) + (odd ? 1u : 0u), p.step, p);
+                    const unsigned r0 = __shfl_xor_sync(0xffffffffu, odd ? blk.w[0] : blk.w[2], 1);
+                    const unsigned r1 = __shfl_xor_sync(0xffffffffu, odd ? blk.w[1] : blk.w[3], 1);
+                    nw[0] = odd ? r0 : blk.w[0];
+                    nw[1] = odd ? r1 : blk.w[1];
+                    keep0 = odd ? blk.w[2] : r0;
+                    keep1 = odd ? blk.w[3] : r1;
+                } else {
+                    nw[0] = keep0;
+                    nw[1] = keep1;
+                }
+            } else if (vec_active) {
+                noise_words<N>(p, (unsigned)(p.gx0 + x), (unsigned)(p.gy0 + y), (unsigned)(p.gz0 + z), nw);
+            }
+        }
         if (vec_active) {
             Vec<T> ou, ov;
-            update_vec<T, ARITH, NOISE>(am, a0, ap, us, un, uw, ue, bm, b0, bp, vs, vn, vw, ve, p, x, y, z, ou, ov);
+            if constexpr (PAIR)
+                update_vec_w<T, ARITH, NOISE>(am, a0, ap, us, un, uw, ue, bm, b0, bp, vs, vn, vw, ve, p, nw, ou, ov);
+            else
+                update_vec<T, ARITH, NOISE>(am, a0, ap, us, un, uw, ue, bm, b0, bp, vs, vn, vw, ve, p, x, y, z, ou, ov);
             store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
             pou += pxy;
             pov += pxy;
@@ -392,19 +461,27 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
 #pragma unroll
     for (int q = 0; q < N; ++q) { ua.a[q] = ub.a[q] = uc.a[q] = va.a[q] = vb.a[q] = vc.a[q] = T(0); }
 
+    // Float64 noise: lanes 2k, 2k+1 share one Philox counter block when the tile starts on a multiple of 4
+    const bool pair_ok = ((p.gx0 + xtile) & 3) == 0;
+    unsigned keep0 = 0u, keep1 = 0u;
+
     int s = 0, sprev = 0;
     unsigned ph = 0;
+    // slot release: every lane has used what it loaded from the slot (the update is computed), one lane
+    // arrives.  XF: the edge lane's boundary-column stores must be ordered before the arrival.
+#ifdef GSB_NO_ELECT
+#define GSB_RELEASE_SLOT(BAR) { __syncwarp(); if (lane == 0) mbar_arrive(BAR); }
+#else
+#define GSB_RELEASE_SLOT(BAR) { if (XF) __syncwarp(); mbar_arrive_one_per_warp(BAR); }
+#endif
     // one step of the ring: wait for plane i, consume (plane i-1 is updated), release plane i-1
 #define GSB_TMA_STEP(AM, A0, AP, BM, B0, BP)                                                              \
     {                                                                                                     \
         mbar_wait(full_bar(s), ph);                                                                       \
         tma_consume<T, ARITH, NOISE, TY, XF>(tiles + s * SB, tiles + sprev * SB, i, AM, A0, AP, BM, B0, BP, roff, eoff, \
                                              lane_w, lane_e, vec_active, p, box, x, y, zs + i - 2, pou, pov, L.pxy,  \
-                                             own_x);                                                      \
-        if (i >= 1) {                                                                                     \
-            __syncwarp();                                                                                 \
-            if (lane == 0) mbar_arrive(empty_bar(sprev));                                                 \
-        }                                                                                                 \
+                                             own_x, pair_ok, keep0, keep1);                               \
+        if (i >= 1) GSB_RELEASE_SLOT(empty_bar(sprev))                                                     \
         sprev = s;                                                                                        \
         if (++s == STAGES) { s = 0; ph ^= 1u; }                                                           \
         ++i;                                                                                              \
@@ -420,6 +497,7 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
         if (i < nplanes) GSB_TMA_STEP(ub, uc, ua, vb, vc, va)
     }
 #undef GSB_TMA_STEP
+#undef GSB_RELEASE_SLOT
 }
 
 // ------------------------------------------------------------------------------------------
