@@ -629,3 +629,25 @@ def test_bench_own_arm_prints_one_json_line():
     assert d["roofline"]["bound"] == "hbm" and abs(d["roofline"]["frac"] - d["roofline"]["achieved"] / d["roofline"]["peak"]) < 1e-9
     assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["e2e"]["d2h_bytes_per_step"] > 0 and d["e2e"]["value"] > 0
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["value"] > 0
+    # round 2: the K steps after warm-up are window 0 = value; later windows and the other arithmetic beside it
+    w = d["windows"]
+    assert w["n"] == 3 and w["value_window"] == 0 and abs(w["ms_per_step"][0] - d["ms_per_step"]) < 1e-12
+    assert len(w["ms_per_step_by_rank_all"]) == 3 and len(w["ms_per_step_by_rank"]) == 1
+    assert d["value_reference_arith"]["value"] > 0 and d["e2e_async"]["value"] > 0 and d["e2e_every_step"]["value"] > 0
+    assert d["config"]["scaling_mode"] == "weak" and d["config"]["per_gpu"] == [128, 128, 128]
+
+
+def test_bench_strong_scaling_mode_one_gpu():
+    """--scaling strong --global-L: sizes = L ./ dims (communication.jl:73); at one GPU the whole cube."""
+    import json
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--scaling", "strong", "--global-L", "96", "--precision",
+                        "Float64", "--steps", "5", "--warmup", "3", "--windows", "1", "--no-e2e", "--no-cpu-baseline"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads([ln for ln in r.stdout.splitlines() if ln.strip()][0])
+    assert d["scaling"] == "strong" and d["dtype"] == "f64" and d["config"]["global"] == [96, 96, 96]
+    assert d["config"]["per_gpu"] == [96, 96, 96] and d["value"] > 0 and "value_reference_arith" not in d
