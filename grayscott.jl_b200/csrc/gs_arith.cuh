@@ -30,6 +30,24 @@ __device__ __forceinline__ double div6_rn(double x) {
     return res;
 }
 
+// The same quotient for the Float64 update kernels, with the rare case split off: the fast path (sign of a
+// zero transferred with one LOP3) plus a flag "x is tiny but not zero" from integer compares on the exponent
+// field; the caller redoes flagged cells with div6_rare, a real call that nvcc cannot evaluate speculatively.
+// One branch per cell instead of one compare + branch region per quotient.
+static __device__ __noinline__ double div6_rare(double x) { return x == 0.0 ? x : __ddiv_rn(x, 6.0); }
+
+__device__ __forceinline__ double div6_fast(double x, bool& rare) {
+    const double c = 0x1.5555555555555p-3;
+    const double q = __dmul_rn(x, c);
+    const double r = __fma_rn(-6.0, q, x);
+    const double res = __fma_rn(r, c, q);
+    const int xh = __double2hiint(x), ah = xh & 0x7fffffff;
+    rare = rare || (ah < 0x0df00000 && (ah | __double2loint(x)) != 0);      // |x| < 2^-800, x != 0
+    int hi;
+    asm("lop3.b32 %0, %1, %2, 0x80000000, 0xD8;" : "=r"(hi) : "r"(__double2hiint(res)), "r"(xh));   // +-0 / 6 = +-0
+    return __hiloint2double(hi, __double2loint(res));
+}
+
 // noise * r with r = ri * 2^-31, ri the integer-valued variate of gs_philox.cuh.  Scaling by a
 // power of two is exact, so RN(noise * r) == RN((noise * 2^-31) * ri) unless noise * 2^-31 leaves
 // the normal range; the host decides (Params::ref_mode) and both forms give the same bits.
@@ -86,8 +104,10 @@ __device__ __forceinline__ void cell_update_ref(float uc, float vc, float su, fl
 template <bool NOISE, int MODE>
 __device__ __forceinline__ void cell_update_ref(double uc, double vc, double su, double sv, double r,
                                                 const Params& p, double& un, double& vn) {
-    const double lap_u = div6_rn(__dsub_rn(su, __dmul_rn(6.0, uc)));
-    const double lap_v = div6_rn(__dsub_rn(sv, __dmul_rn(6.0, vc)));
+    const double xu = __dsub_rn(su, __dmul_rn(6.0, uc)), xv = __dsub_rn(sv, __dmul_rn(6.0, vc));
+    bool rare = false;
+    double lap_u = div6_fast(xu, rare), lap_v = div6_fast(xv, rare);
+    if (rare) { lap_u = div6_rare(xu); lap_v = div6_rare(xv); }   // a thin shell of cells at most
     const double uvv = __dmul_rn(uc, __dmul_rn(vc, vc));
     const double fkv = __dmul_rn(p.FK, vc);
     double du = __dsub_rn(__dmul_rn(p.Du, lap_u), uvv);

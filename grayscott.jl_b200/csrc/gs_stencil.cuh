@@ -261,7 +261,7 @@ struct TmaTile {
 // The caller rotates the register names (three-way unrolled loop), so no register moves.
 // XF: an edge lane that owns a subdomain boundary column (own_x) finds its x ghost at `eoff` in the side
 // area of the slot (put there by the producer) and leaves its new boundary value at eoff + 2 * TY.
-template <typename T, int ARITH, bool NOISE, int TY, bool XF>
+template <typename T, int ARITH, bool NOISE, int TY, bool XF, bool UPD>
 __device__ __forceinline__ void tma_consume(const unsigned char* cur, unsigned char* prev, int i,
                                             const Vec<T>& am, const Vec<T>& a0, Vec<T>& ap, const Vec<T>& bm,
                                             const Vec<T>& b0, Vec<T>& bp, const int roff, const int eoff,
@@ -276,15 +276,16 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, unsigned c
     const T* sv_ = reinterpret_cast<const T*>(cur + FB);
     ap = ld_vec(su_ + roff);
     bp = ld_vec(sv_ + roff);
-    if (i >= 2) {
+    if constexpr (UPD) {                     // planes 0 and 1 of a chunk only fill the register pipeline
         T* pu_ = reinterpret_cast<T*>(prev);
         T* pv_ = reinterpret_cast<T*>(prev + FB);
         const Vec<T> us = ld_vec(pu_ + roff - Tile::BW), un = ld_vec(pu_ + roff + Tile::BW);
         const Vec<T> vs = ld_vec(pv_ + roff - Tile::BW), vn = ld_vec(pv_ + roff + Tile::BW);
         // x neighbours across vectors: shuffles inside the warp; lanes 0 and 31 take the scalar at eoff
         // (the box halo, or the side area when the column beyond is a neighbour's)
-        T eu = T(0), ev = T(0);
-        if (lane_w || lane_e) { eu = pu_[eoff]; ev = pv_[eoff]; }
+        // (every lane loads: for lanes 1..30 eoff is simply the next lane's first element, unused -- two
+        // conflicted LDS cost less than the divergent region around them did)
+        const T eu = pu_[eoff], ev = pv_[eoff];
         const T su = __shfl_up_sync(0xffffffffu, a0.a[N - 1], 1), sd = __shfl_down_sync(0xffffffffu, a0.a[0], 1);
         const T tu = __shfl_up_sync(0xffffffffu, b0.a[N - 1], 1), td = __shfl_down_sync(0xffffffffu, b0.a[0], 1);
         const T uw = lane_w ? eu : su, ue = lane_e ? eu : sd;
@@ -475,10 +476,10 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
 #define GSB_RELEASE_SLOT(BAR) { if (XF) __syncwarp(); mbar_arrive_one_per_warp(BAR); }
 #endif
     // one step of the ring: wait for plane i, consume (plane i-1 is updated), release plane i-1
-#define GSB_TMA_STEP(AM, A0, AP, BM, B0, BP)                                                              \
+#define GSB_TMA_STEP(UPD, AM, A0, AP, BM, B0, BP)                                                         \
     {                                                                                                     \
         mbar_wait(full_bar(s), ph);                                                                       \
-        tma_consume<T, ARITH, NOISE, TY, XF>(tiles + s * SB, tiles + sprev * SB, i, AM, A0, AP, BM, B0, BP, roff, eoff, \
+        tma_consume<T, ARITH, NOISE, TY, XF, UPD>(tiles + s * SB, tiles + sprev * SB, i, AM, A0, AP, BM, B0, BP, roff, eoff, \
                                              lane_w, lane_e, vec_active, p, box, x, y, zs + i - 2, pou, pov, L.pxy,  \
                                              own_x, pair_ok, keep0, keep1);                               \
         if (i >= 1) GSB_RELEASE_SLOT(empty_bar(sprev))                                                     \
@@ -487,14 +488,16 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
         ++i;                                                                                              \
     }
     int i = 0;
+    GSB_TMA_STEP(false, ua, ub, uc, va, vb, vc)          // planes zs-1 and zs: nothing to update yet
+    GSB_TMA_STEP(false, ub, uc, ua, vb, vc, va)
     while (i + 3 <= nplanes) {
-        GSB_TMA_STEP(ua, ub, uc, va, vb, vc)
-        GSB_TMA_STEP(ub, uc, ua, vb, vc, va)
-        GSB_TMA_STEP(uc, ua, ub, vc, va, vb)
+        GSB_TMA_STEP(true, uc, ua, ub, vc, va, vb)
+        GSB_TMA_STEP(true, ua, ub, uc, va, vb, vc)
+        GSB_TMA_STEP(true, ub, uc, ua, vb, vc, va)
     }
     if (i < nplanes) {
-        GSB_TMA_STEP(ua, ub, uc, va, vb, vc)
-        if (i < nplanes) GSB_TMA_STEP(ub, uc, ua, vb, vc, va)
+        GSB_TMA_STEP(true, uc, ua, ub, vc, va, vb)
+        if (i < nplanes) GSB_TMA_STEP(true, ua, ub, uc, va, vb, vc)
     }
 #undef GSB_TMA_STEP
 #undef GSB_RELEASE_SLOT

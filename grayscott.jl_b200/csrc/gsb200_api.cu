@@ -239,9 +239,9 @@ static void default_kernel(gsb_handle* h) {
         k.kind = KERNEL_TMA_HI; k.ty = 8;
         if (nz) { k.stages = 6; k.zchunk = 32; } else { k.stages = 4; k.zchunk = 16; }
     } else {
-        // Float32 reference arithmetic (FP64-pipe and conversion bound): the lower occupancy class, no spills
-        k.kind = KERNEL_TMA_LO;
-        if (nz) { k.ty = 8; k.stages = 4; k.zchunk = 64; } else { k.ty = 4; k.stages = 8; k.zchunk = 64; }
+        // Float32 reference arithmetic (FP64-pipe and conversion bound); re-measured after the consumer loop
+        // lost its prologue test and most of its spills: the higher occupancy class wins again
+        k.kind = KERNEL_TMA_HI; k.ty = 8; k.stages = 4; k.zchunk = 64;
     }
     // small grids: more, smaller CTAs (measured at L = 256: 4 rows per CTA beats 8 by 6 %)
     if ((long long)h->L.sx * h->L.sy * h->L.sz <= 300ll * 300 * 300 && (k.dtype == DT_F64 || k.arith == ARITH_NATIVE)) {

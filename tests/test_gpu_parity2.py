@@ -329,3 +329,27 @@ def test_pdf_ignores_nan_and_large_slices(sim, prec):
     assert np.array_equal(pdf, want)
     assert pdf.sum() == sizes[0] * sizes[1] * sizes[2] - 3
     f.close()
+
+
+@pytest.mark.parametrize("kern", KERNELS)
+def test_float64_tiny_and_signed_zero_quotients(sim, orc, kern):
+    """The exact divide-by-6 of the Float64 path has a rare branch (|x| < 2^-800, x != 0: true division) and a
+    sign rule (+-0 / 6 = +-0).  Fields made of +0, -0, subnormals and values down to 1e-320 drive both on
+    every kernel shape; compared with the oracle as BIT PATTERNS (-0 == +0 would hide a wrong sign)."""
+    rng = np.random.default_rng(99)
+    sizes = (70, 11, 6)
+    shape = (sizes[2] + 2, sizes[1] + 2, sizes[0] + 2)
+    pool = np.array([0.0, -0.0, 1e-300, -3e-310, 5e-324, 1e-250, -1e-245, 2.5e-320, 1.0, 1e-241], np.float64)
+    u = pool[rng.integers(0, len(pool), shape)]
+    v = pool[rng.integers(0, len(pool), shape)]
+    s, mcd, f = custom_fields(sim, sizes, "Float64")
+    f.set_kernel(*kern)
+    f.u.set(u)
+    f.v.set(v)
+    sim.calculate(f, s, mcd)
+    ut, vt = np.asarray(f.u_temp), np.asarray(f.v_temp)
+    f.close()
+    eu, ev = orc.calculate_arrays(u, v, **PHYS)
+    inner = (slice(1, -1),) * 3
+    assert np.array_equal(ut[inner].view(np.uint64), eu[inner].view(np.uint64))
+    assert np.array_equal(vt[inner].view(np.uint64), ev[inner].view(np.uint64))

@@ -1,0 +1,15 @@
+#!/bin/bash
+# r2 probe 15: prologue iterations peeled off the consumer loop, edge scalars loaded by every lane
+cd "${GRAFT_REPO_ROOT:-/root/repo}"; mkdir -p gpurun_out
+O=gpurun_out/p15
+T=grayscott.jl_b200/gs_tune
+$T 1024 f32 native 1 10 tmahi:8:6:32 tmahi:8:4:32 tmahi:8:6:64 tmahi:8:6:32 > ${O}_nat1.log 2>&1
+$T 1024 f32 native 0 10 tmahi:8:4:16 tmahi:8:4:32 tmahi:8:6:32 > ${O}_nat0.log 2>&1
+$T 1024 f32 ref 1 10 tmalo:8:4:64 tmahi:8:4:64 tmalo:4:8:64 > ${O}_ref1.log 2>&1
+$T 1024 f32 ref 0 10 tmalo:4:8:64 tmahi:8:4:64 > ${O}_ref0.log 2>&1
+$T 768 f64 ref 1 10 tmalo:4:4:32 tmalo:8:6:32 > ${O}_f64_1.log 2>&1
+$T 768 f64 ref 0 10 tmalo:8:6:32 > ${O}_f64_0.log 2>&1
+sleep 3
+$T 1024 f32 native 1 300 tmahi:8:6:32 > ${O}_sustained_nat1.log 2>&1
+timeout 2400 python -m pytest tests -x -q -m gpu > ${O}_pytest.log 2>&1; echo "pytest rc=$?" >> ${O}_pytest.log
+echo done
