@@ -106,7 +106,17 @@ __device__ __forceinline__ void update_vec_w(const Vec<T>& um, const Vec<T>& u0,
     }
 }
 
-// Store the cells of a vector that fall inside [bx0, bx1).
+// Store the cells of a vector that fall inside [bx0, bx1).  The partial case (a box edge that cuts a
+// vector) is a real call: kept inline, its address arithmetic made nvcc carry a second copy of the running
+// pointers through the hot loop.
+template <typename T>
+static __device__ __noinline__ void store_partial(T* pu, T* pv, Vec<T> uo, Vec<T> vo, int x, int bx0, int bx1) {
+    constexpr int N = Vec<T>::N;
+#pragma unroll
+    for (int i = 0; i < N; ++i)
+        if (x + i >= bx0 && x + i < bx1) { pu[i] = uo.a[i]; pv[i] = vo.a[i]; }
+}
+
 template <typename T>
 __device__ __forceinline__ void store_masked(T* pu, T* pv, const Vec<T>& uo, const Vec<T>& vo, int x, int bx0,
                                              int bx1) {
@@ -115,9 +125,7 @@ __device__ __forceinline__ void store_masked(T* pu, T* pv, const Vec<T>& uo, con
         st_vec_stream(pu, uo);
         st_vec_stream(pv, vo);
     } else {
-#pragma unroll
-        for (int i = 0; i < N; ++i)
-            if (x + i >= bx0 && x + i < bx1) { pu[i] = uo.a[i]; pv[i] = vo.a[i]; }
+        store_partial<T>(pu, pv, uo, vo, x, bx0, bx1);
     }
 }
 
@@ -267,7 +275,7 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, unsigned c
                                             const Vec<T>& b0, Vec<T>& bp, const int roff, const int eoff,
                                             const bool lane_w, const bool lane_e, const bool vec_active,
                                             const Params& p, const Box& box, const int x, const int y, const int z,
-                                            T*& pou, T*& pov, const long long pxy, const bool own_x,
+                                            T*& pou, const long long vdelta, const long long pxy, const bool own_x,
                                             const bool pair_ok, unsigned& keep0, unsigned& keep1) {
     using Tile = TmaTile<T, TY>;
     constexpr int N = Tile::N;
@@ -323,9 +331,9 @@ __device__ __forceinline__ void tma_consume(const unsigned char* cur, unsigned c
                 update_vec_w<T, ARITH, NOISE>(am, a0, ap, us, un, uw, ue, bm, b0, bp, vs, vn, vw, ve, p, nw, ou, ov);
             else
                 update_vec<T, ARITH, NOISE>(am, a0, ap, us, un, uw, ue, bm, b0, bp, vs, vn, vw, ve, p, x, y, z, ou, ov);
-            store_masked(pou, pov, ou, ov, x, box.x0, box.x1);
+            // one running pointer; v's array lies a kernel-uniform distance away
+            store_masked(pou, reinterpret_cast<T*>(reinterpret_cast<char*>(pou) + vdelta), ou, ov, x, box.x0, box.x1);
             pou += pxy;
-            pov += pxy;
             if (XF && own_x) {                                   // my boundary column, for the producer to send
                 pu_[eoff + 2 * TY] = lane_w ? ou.a[0] : ou.a[N - 1];
                 pv_[eoff + 2 * TY] = lane_w ? ov.a[0] : ov.a[N - 1];
@@ -450,7 +458,7 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
     const bool vec_active = row_active && x < box.x1 && x + N > box.x0;
     const long long out0 = vec_active ? L.idx(x, y, zs) : 0;
     T* pou = uo + out0;
-    T* pov = vo + out0;
+    const long long vdelta = reinterpret_cast<const char*>(vo) - reinterpret_cast<const char*>(uo);
     const int roff = (w + 1) * Tile::BW + N + lane * N;  // my centre vector in the box (elements)
     const bool lane_w = lane == 0, lane_e = lane == 31;
     // the lane that owns column 0 / sx-1 of a row whose x neighbour is another subdomain
@@ -480,7 +488,7 @@ stencil_tma_kernel(const __grid_constant__ CUtensorMap map_u, const __grid_const
     {                                                                                                     \
         mbar_wait(full_bar(s), ph);                                                                       \
         tma_consume<T, ARITH, NOISE, TY, XF, UPD>(tiles + s * SB, tiles + sprev * SB, i, AM, A0, AP, BM, B0, BP, roff, eoff, \
-                                             lane_w, lane_e, vec_active, p, box, x, y, zs + i - 2, pou, pov, L.pxy,  \
+                                             lane_w, lane_e, vec_active, p, box, x, y, zs + i - 2, pou, vdelta, L.pxy, \
                                              own_x, pair_ok, keep0, keep1);                               \
         if (i >= 1) GSB_RELEASE_SLOT(empty_bar(sprev))                                                     \
         sprev = s;                                                                                        \

@@ -408,7 +408,7 @@ static int create_impl(gsb_handle* h, const gsb_config* cfg) {
         const char* hc = getenv("GSB_HALO_CHUNKS");
         h->halo_chunks = hc ? atoi(hc) : 0;
         const char* fx = getenv("GSB_FUSE_X");
-        h->fuse_x = fx ? atoi(fx) : 2;
+        h->fuse_x = fx ? atoi(fx) : 1;
     }
     for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&h->tev[i]));
     for (int k = 0; k <= GSB_MAX_CHUNKS; ++k)
@@ -872,8 +872,9 @@ static bool interior_box(const gsb_handle* h, Box* b) {
 // 16-byte vectors: the producer warps of the first / last x tile fetch the neighbour's column from the
 // dense receive buffer and send the new boundary column to the dense message buffer with bulk copies.
 // That removes the strided pack / unpack of 2 * sy * sz cells (a 128-byte DRAM line per 4-byte cell).
-// $GSB_FUSE_X at gsb_create: 2 (default) the x-face instantiation runs on the first / last x tile only,
-// 1 on the whole chunk, 0 off (the strided kernels then carry the x faces as well).
+// $GSB_FUSE_X at gsb_create: 1 (default) one launch per chunk, every CTA runs the x-face instantiation (it no
+// longer spills, and only the edge tiles act on it); 2 the x-face instantiation on the first / last x tile only,
+// the plain kernel in between; 0 off (the strided kernels then carry the x faces as well).
 static bool fused_x(const gsb_handle* h) {
     const int tile = 32 * (int)(16 / h->es);
     return h->fuse_x != 0 && h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
@@ -1102,9 +1103,8 @@ static int pipeline_compute_chunk(gsb_handle* h, int k, int C, const Params& p, 
             // one launch, every CTA runs the x-face instantiation (only the edge tiles act on it)
             if (launch_box(h, Box{0, sx, 0, sy, pc.z0, pc.z1}, p, st, &xf)) return 1;
         } else {
-            // the x-face instantiation on the first / last x tile only, the plain kernel in between: where
-            // the former is slower (it spills at the register cap of the noisy variants) it now touches
-            // 1/8 .. 2/8 of the cells instead of all of them
+            // the x-face instantiation on the first / last x tile only, the plain kernel in between (was the
+            // better choice while that instantiation spilled at the register cap of the noisy variants)
             int lo = 0, hi = sx;
             if (xf.send_lo) {
                 XFaceArgs a = xf; a.send_hi = nullptr; a.ghost_hi = nullptr;
