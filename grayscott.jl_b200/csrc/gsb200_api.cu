@@ -237,7 +237,9 @@ static void default_kernel(gsb_handle* h) {
         if (nz) { k.ty = 4; k.stages = 4; k.zchunk = 32; } else { k.ty = 8; k.stages = 6; k.zchunk = 32; }
     } else if (k.arith == ARITH_NATIVE) {
         k.kind = KERNEL_TMA_HI; k.ty = 8;
-        if (nz) { k.stages = 6; k.zchunk = 32; } else { k.stages = 4; k.zchunk = 16; }
+        // with noise: 4 ring slots win the 20-step measurement by 5 % (2.89 against 3.05 ms at L = 1024) and lose
+        // 1 % over 300 steps (3.04 against 3.01 ms) since the consumer loop was trimmed (profiles/r2_tuning_raw.log)
+        if (nz) { k.stages = 4; k.zchunk = 32; } else { k.stages = 4; k.zchunk = 16; }
     } else {
         // Float32 reference arithmetic (FP64-pipe and conversion bound); re-measured after the consumer loop
         // lost its prologue test and most of its spills: the higher occupancy class wins again
@@ -877,6 +879,10 @@ static bool interior_box(const gsb_handle* h, Box* b) {
 // the plain kernel in between; 0 off (the strided kernels then carry the x faces as well).
 static bool fused_x(const gsb_handle* h) {
     const int tile = 32 * (int)(16 / h->es);
+    // in-process ranks on DIFFERENT devices keep the strided pack kernel for the x faces: its plain stores into
+    // the neighbour GPU's receive buffer are the tested peer path, a bulk store from shared memory to a peer is not
+    for (int d = GSB_WEST; d <= GSB_EAST; ++d)
+        if (h->transport == TR_LOCAL && h->active[d] && h->peer[d] && h->peer[d]->device != h->device) return false;
     return h->fuse_x != 0 && h->halo_mode == HALO_PIPELINE && h->kcfg.kind != KERNEL_L1 &&
            (h->active[GSB_WEST] || h->active[GSB_EAST]) && h->L.sx % tile == 0 && h->L.sy % (int)(16 / h->es) == 0;
 }

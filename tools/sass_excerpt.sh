@@ -2,12 +2,12 @@
 # Writes profiles/r2_sass_excerpt_headline.txt from the built library: the instructions that show what the
 # headline kernel is made of (TMA tensor loads, bulk copies, mbarrier ops, LDS.128, STG.128, elect, Philox).
 cd "$(dirname "$0")/.."
-K='_ZN3gsb18stencil_tma_kernelIfLi1ELb1ELi8ELi6ELi3ELb1EEEv14CUtensorMap_stS1_PT_S3_NS_6LayoutENS_6ParamsENS_3BoxEiNS_9XFaceArgsE'
+K='_ZN3gsb18stencil_tma_kernelIfLi1ELb1ELi8ELi4ELi3ELb1EEEv14CUtensorMap_stS1_PT_S3_NS_6LayoutENS_6ParamsENS_3BoxEiNS_9XFaceArgsE'
 S=/tmp/headline_xf.sass
 cuobjdump -sass -fun "$K" grayscott.jl_b200/libgsb200.so 2>/dev/null | sed -E 's#\s*/\* 0x[0-9a-f]+ \*/##' | grep -E "^\s+/\*[0-9a-f]{4}\*/" > $S
 {
 echo "# SASS excerpt of the headline kernel as shipped in grayscott.jl_b200/libgsb200.so (sm_100a):"
-echo "#   stencil_tma_kernel<float, ARITH_NATIVE, noise, TY=8, STAGES=6, 3 CTAs/SM, XF=true>   (XF=false: same without UBLKCP)"
+echo "#   stencil_tma_kernel<float, ARITH_NATIVE, noise, TY=8, STAGES=4, 3 CTAs/SM, XF=true>   (XF=false: same without UBLKCP)"
 echo "#   cuobjdump -sass -fun '$K' grayscott.jl_b200/libgsb200.so      ($(wc -l < $S) instructions)"
 echo "#   ptxas: $(grep -A3 "$K" build/csrc/gs_stencil_f32.ptxas.log | grep -E "Used|spill" | tr -s ' ' | tr '\n' ';')"
 echo "# Counts over the whole kernel:"
