@@ -416,6 +416,8 @@ def parity_report(cx, L=192, steps=12):
     criterion) and (b) with the CPU oracle's N-rank run (oracle = checker only)."""
     import numpy as np
     torch, sim = cx.torch, cx.sim
+    if any(L % d for d in dims_create(cx.world)):
+        return {"ok": None, "skipped": f"L = {L} does not divide by dims {dims_create(cx.world)}"}
     cases = []
     ok_all = True
     for precision, arith, halo in (("Float32", "reference", "pipeline"), ("Float32", "reference", "split"),
