@@ -38,8 +38,10 @@ __device__ __forceinline__ Philox4 philox4x32_10(unsigned c0, unsigned c1, unsig
 
 __device__ __forceinline__ double noise_r64(unsigned word) {
     // r = -1 + 2*(word * 2^-32) = ri * 2^-31 with ri = word - 2^31; returns ri (exact), the caller
-    // applies the 2^-31 (gs_arith.cuh noise_term)
-    return (double)(int)(word ^ 0x80000000u);
+    // applies the 2^-31 (gs_arith.cuh noise_term).  The integer becomes a double without a conversion
+    // instruction: the bit pattern 0x43300000'word is exactly 2^52 + word, and subtracting 2^52 + 2^31 is exact
+    // (an I2F.F64 costs ~5.5 dispatch clocks on B200, a DADD 2.2: profiles/r2_pipe_throughputs.txt).
+    return __dadd_rn(__hiloint2double(0x43300000, (int)word), -4503601774854144.0);
 }
 __device__ __forceinline__ float noise_r32(unsigned word) {
     // the integer-valued variate r32 * 2^23 in [-2^23, 2^23); cell_update_native multiplies it by
